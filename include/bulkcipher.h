@@ -1,0 +1,147 @@
+/*
+ * bulkcipher.h — the B200 bulk-cipher engine's own C-ABI (extension symbols).
+ *
+ * The drop-in symbols of the reference live in aes.h / aesni.h / arc4.h /
+ * rc4.h next to this file and are implemented on top of the calls below.
+ * These bc_* entry points are what the BASELINE configs force beyond the
+ * reference API (SURVEY §8b "Extensions the configs force"): device-resident
+ * buffers, size_t lengths, an explicit starting block for CTR shards, batched
+ * CBC-encrypt and batched RC4.  Plain pointers and sizes only; `stream` is a
+ * cudaStream_t passed as void* (NULL = the default stream).
+ *
+ * Every function returns 0 on success or a negative BC_ERR_* code;
+ * bc_last_error() gives the calling thread's last message.  There is no CPU
+ * fallback anywhere: without a usable CUDA device every call fails with
+ * BC_ERR_CUDA / BC_ERR_NO_DEVICE.
+ *
+ * Round keys (`rk`) are 4*(nr+1) little-endian 32-bit words = the low halves
+ * of aes_context.rk[] (aes-modes/aes.h:41-47), i.e. exactly the packed
+ * schedule aesni.c consumes (aes-modes/aesni.c:79-97).  `rk` is a HOST pointer;
+ * it travels to the GPU as a kernel argument (constant bank), so calls are
+ * re-entrant and no global key state exists.
+ */
+#ifndef BULKCIPHER_H
+#define BULKCIPHER_H
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define BC_OK             0
+#define BC_ERR_CUDA       (-0x7001)  /* a CUDA runtime call or launch failed        */
+#define BC_ERR_BAD_ARG    (-0x7002)  /* NULL pointer, bad nr / mode / length         */
+#define BC_ERR_NO_DEVICE  (-0x7003)  /* no CUDA device visible                       */
+#define BC_ERR_OVERLAP    (-0x7004)  /* in/out partially overlap (must be == or disjoint) */
+#define BC_ERR_TOO_LARGE  (-0x7005)  /* request exceeds a documented fixed limit     */
+
+#define BC_ENCRYPT 1                 /* == AES_ENCRYPT, aes-modes/aes.h:33 */
+#define BC_DECRYPT 0                 /* == AES_DECRYPT, aes-modes/aes.h:34 */
+
+const char *bc_last_error(void);
+int  bc_device_count(void);
+/* Device used by the calling thread's *_host calls and allocations (default 0). */
+int  bc_set_device(int device);
+int  bc_get_device(void);
+int  bc_sm_count(void);
+
+/* ---- memory helpers for C callers (harness, multi-GPU driver) ------------ */
+void *bc_host_alloc(size_t bytes);            /* pinned host memory (cudaHostAlloc)   */
+void  bc_host_free(void *p);
+void *bc_dev_alloc(size_t bytes);
+void  bc_dev_free(void *p);
+int   bc_memcpy_h2d(void *d_dst, const void *h_src, size_t bytes);
+int   bc_memcpy_d2h(void *h_dst, const void *d_src, size_t bytes);
+int   bc_device_sync(void);
+
+/* ---- AES on device-resident buffers -------------------------------------- */
+
+/* CTR keystream XOR.  Replaces the loop of aes_crypt_ctr (aes-modes/aes.c:869-900)
+ * and AES_CTR_encrypt (aes-modes/aesni.c:120-152) for a buffer already in HBM.
+ * Block i of the buffer uses counter = `counter` (16 bytes, big-endian integer)
+ * + first_block + i.  counter_bits = 128: full 128-bit carry (aes.c:884-888);
+ * counter_bits = 64: the add wraps inside bytes 8..15 and never carries into
+ * bytes 0..7 (_mm_add_epi64, aesni.c:139,143).  nbytes need not be a multiple of
+ * 16 (the last block is used partially, like aes.c:879-895).  If
+ * d_last_keystream != NULL it receives the 16-byte keystream block of the last
+ * block touched (the reference's stream_block on return).  in == out allowed. */
+int bc_aes_ctr_dev(const uint32_t *rk, int nr, const unsigned char counter[16], int counter_bits,
+                   uint64_t first_block, const void *d_in, void *d_out, size_t nbytes,
+                   void *d_last_keystream, void *stream);
+
+/* ECB over nbytes/16 whole blocks.  Replaces the per-block loop over
+ * aes_crypt_ecb (aes-modes/aes.c:650-752, harness aes-modes/test.c:37-41) and
+ * AES_ECB_encrypt / AES_ECB_decrypt (aes-modes/aesni.c:79-118).  `mode` selects
+ * the tables only; rk must be the matching (enc or equivalent-inverse dec)
+ * schedule, exactly as in the reference (aes.c:677,711).  in == out allowed. */
+int bc_aes_ecb_dev(const uint32_t *rk, int nr, int mode, const void *d_in, void *d_out,
+                   size_t nbytes, void *stream);
+
+/* CBC decrypt, parallel over blocks.  Replaces aes_crypt_cbc(AES_DECRYPT)
+ * (aes-modes/aes.c:784-797).  iv (host, 16 bytes) is read only; the caller gets
+ * the new iv as the last ciphertext block (aes.c:792).  in == out is allowed
+ * and then uses a library-owned scratch buffer in HBM (16 bytes per 4 KiB of
+ * input) to keep the chunk-boundary ciphertext blocks. */
+int bc_aes_cbc_decrypt_dev(const uint32_t *rk, int nr, const unsigned char iv[16],
+                           const void *d_in, void *d_out, size_t nbytes, void *stream);
+
+/* CBC encrypt of n_msgs independent messages of msg_len bytes each (multiple
+ * of 16), message-major contiguous.  Each message is one aes_crypt_cbc(
+ * AES_ENCRYPT) call of the reference (aes-modes/aes.c:801-812): serial inside a
+ * message, parallel across messages.  d_ivs is [n_msgs][16]; if d_ivs_out !=
+ * NULL it receives each message's last ciphertext block (aes.c:807). */
+int bc_aes_cbc_encrypt_batch_dev(const uint32_t *rk, int nr, size_t n_msgs, size_t msg_len,
+                                 const void *d_ivs, void *d_ivs_out,
+                                 const void *d_in, void *d_out, void *stream);
+
+/* ---- RC4 / ARC4 on device-resident buffers ------------------------------- */
+
+/* n_streams independent RC4 streams, stream-major contiguous: for stream s,
+ * key = d_keys[s*keylen .. +keylen), data = d_in[s*length .. +length).  Each
+ * stream is arc4_setup -> arc4_prep(length) -> arc4_crypt (arc4.c:43-112) =
+ * rc4_init -> rc4_crypt (rc4.c:56-99, intended semantics), KSA+PRGA+XOR fused.
+ * If d_ctx_out != NULL it receives n_streams arc4_context structs (264 bytes:
+ * int x, int y, m[256]; arc4.h:35-41) holding the state after `length` bytes.
+ * If d_ctx_in != NULL the KSA is skipped and streams resume from those
+ * contexts (keys ignored).  1 <= keylen <= 256.  in == out allowed. */
+int bc_arc4_batch_dev(size_t n_streams, const void *d_keys, unsigned keylen, size_t length,
+                      const void *d_in, void *d_out, const void *d_ctx_in, void *d_ctx_out,
+                      void *stream);
+
+/* out = a ^ b: the whole of arc4_crypt once a keystream exists (arc4.c:101-112).
+ * The three buffers may alias elementwise. */
+int bc_xor_dev(const void *d_a, const void *d_b, void *d_out, size_t nbytes, void *stream);
+
+/* ---- the same operations on HOST buffers --------------------------------- */
+/* Chunked, multi-stream H2D -> kernel -> D2H pipeline through library-owned
+ * device buffers.  Buffers from bc_host_alloc / cudaHostRegister are DMA'd
+ * directly; pageable memory is staged through internal pinned buffers.  These
+ * are what the drop-in symbols call; they are PCIe-bound. */
+int bc_aes_ctr_host(const uint32_t *rk, int nr, const unsigned char counter[16], int counter_bits,
+                    uint64_t first_block, const void *in, void *out, size_t nbytes,
+                    unsigned char last_keystream[16]);
+int bc_aes_ecb_host(const uint32_t *rk, int nr, int mode, const void *in, void *out, size_t nbytes);
+int bc_aes_cbc_decrypt_host(const uint32_t *rk, int nr, const unsigned char iv[16],
+                            const void *in, void *out, size_t nbytes);
+int bc_aes_cbc_encrypt_batch_host(const uint32_t *rk, int nr, size_t n_msgs, size_t msg_len,
+                                  const void *ivs, void *ivs_out, const void *in, void *out);
+/* in == NULL (here and in bc_arc4_batch_dev): write the raw keystream, which is
+ * what arc4_prep produces (arc4.c:72-97).  length == 0 with ctx_out: key setup only. */
+int bc_arc4_batch_host(size_t n_streams, const void *keys, unsigned keylen, size_t length,
+                       const void *in, void *out, const void *ctx_in, void *ctx_out);
+int bc_xor_host(const void *a, const void *b, void *out, size_t nbytes);
+
+/* ---- multi-GPU (one host thread per GPU, no collective) ------------------ */
+/* AES-CTR over a host buffer sharded across n_gpus devices by contiguous block
+ * ranges: GPU g encrypts blocks [g*B/G, (g+1)*B/G) with its
+ * counter offset by the first block index; the last GPU takes the remainder.
+ * Equivalent to one bc_aes_ctr_host call. */
+int bc_aes_ctr_host_multi(int n_gpus, const uint32_t *rk, int nr, const unsigned char counter[16],
+                          int counter_bits, const void *in, void *out, size_t nbytes);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* BULKCIPHER_H */

@@ -1,0 +1,650 @@
+/*
+ * bc_aes.cu — AES-128/192/256 ECB / CBC / CTR kernels for sm_100a and their
+ * extern "C" launchers (the device-pointer half of include/bulkcipher.h).
+ *
+ * Written from scratch for B200; not a port of the reference's
+ * aes-gpu/Source/AES.cu.  Results are bit-exact with the reference's aes.c /
+ * aesni.c (checked against oracle/ in tests/).
+ *
+ * Design (DESIGN.md §3 has the numbers):
+ *  - Integer / shared-memory work, no tensor cores.  One AES round of one
+ *    block is 16 table lookups; the shared-memory pipe serves 32 lanes per
+ *    clock per SM, which is the roofline that binds (not HBM).
+ *  - T-tables FT0..FT3 (aes.c:409-422) live in shared memory replicated once
+ *    per bank: word (i, table, lane) sits at byte  i*256 + (table&1)*128 +
+ *    lane*4  of array table>>1, so lane L only ever touches bank L and every
+ *    warp-wide lookup is one conflict-free wavefront.  With this layout a
+ *    lookup address is ONE PRMT: the state byte lands in address byte 1, the
+ *    lane offset in byte 0; the table select rides in the LDS immediate.
+ *  - Same little-endian column words as aes.c (GET_ULONG_LE, aes.c:42-49): a
+ *    128-bit global load is the state, no byte swaps.
+ *  - Round keys arrive as a __grid_constant__ kernel argument (constant bank),
+ *    so XORs take them as direct operands and launches are re-entrant.
+ *  - CTR: counters are generated in registers from the block index.  Work is
+ *    cut into groups of 256 consecutive counter values (only the last counter
+ *    byte varies inside a group), so 15 of round 1's 16 lookups and 12 of
+ *    round 2's 16 are per-group constants (AES_FROUND index pattern,
+ *    aes.c:603-621): 133 instead of 160 lookups per AES-128 block.  Lane i of
+ *    a warp precomputes the constants of the warp's i-th group; they are
+ *    broadcast with shuffles.
+ *  - Persistent grid: one 512-thread CTA per SM (tables fill 128 KB), warps
+ *    stride over 4 KiB row-groups; global traffic is 128-bit, coalesced
+ *    (a warp row = 512 contiguous bytes), streaming (evict-first) hints.
+ */
+#include <cuda_runtime.h>
+#include <stdint.h>
+
+#include "bulkcipher.h"
+#include "bc_internal.h"
+#include "bc_sbox.inc"
+
+namespace {
+
+__constant__ uint8_t c_sbox[256]     = { BC_SBOX_INIT };
+__constant__ uint8_t c_inv_sbox[256] = { BC_INV_SBOX_INIT };
+
+constexpr int kThreads      = 512;
+constexpr int kWarps        = kThreads / 32;
+constexpr int kArrayBytes   = 65536;           /* two interleaved tables */
+constexpr int kEncSmemBytes = 2 * kArrayBytes; /* FT0|FT1, FT2|FT3 */
+constexpr int kDecSmemBytes = 3 * kArrayBytes; /* RT0|RT1, RT2|RT3, RSb×4|unused */
+constexpr int kRowsPerGroup = 8;               /* 8 rows × 32 lanes = 256 blocks = 4 KiB */
+constexpr int kGroupsPerChunk = 8;             /* CTR: groups handled per warp trip */
+
+struct AesSched { uint32_t rk[60]; };
+
+/* byte offsets of the tables inside dynamic shared memory */
+constexpr int OFF_T0 = 0, OFF_T1 = 128, OFF_T2 = kArrayBytes, OFF_T3 = kArrayBytes + 128;
+constexpr int OFF_SB = 2 * kArrayBytes;
+
+__device__ __forceinline__ uint32_t rotl32(uint32_t v, int n) { return __funnelshift_l(v, v, n); }
+__device__ __forceinline__ uint32_t xtime8(uint32_t x) { return ((x << 1) ^ ((x & 0x80u) ? 0x1bu : 0u)) & 0xffu; }
+
+/* FT0[i] = {02,01,01,03}·S(i), low byte first (aes.c:415-418) */
+__device__ __forceinline__ uint32_t ft0_word(uint32_t i)
+{
+    uint32_t s = c_sbox[i], d = xtime8(s);
+    return d | (s << 8) | (s << 16) | ((d ^ s) << 24);
+}
+
+/* RT0[i] = {0E,09,0D,0B}·S^-1(i), low byte first (aes.c:426-429) */
+__device__ __forceinline__ uint32_t rt0_word(uint32_t i)
+{
+    uint32_t q = c_inv_sbox[i], q2 = xtime8(q), q4 = xtime8(q2), q8 = xtime8(q4);
+    return (q8 ^ q4 ^ q2) | ((q8 ^ q) << 8) | ((q8 ^ q4 ^ q) << 16) | ((q8 ^ q2 ^ q) << 24);
+}
+
+template <bool DEC>
+__device__ __forceinline__ void fill_tables(uint32_t *sm)
+{
+    for (uint32_t idx = threadIdx.x; idx < 256u * 32u; idx += blockDim.x) {
+        uint32_t i = idx >> 5, l = idx & 31u;   /* i is warp-uniform: constant-cache broadcast */
+        uint32_t w = DEC ? rt0_word(i) : ft0_word(i);
+        sm[i * 64 + l]              = w;
+        sm[i * 64 + 32 + l]         = rotl32(w, 8);
+        sm[16384 + i * 64 + l]      = rotl32(w, 16);
+        sm[16384 + i * 64 + 32 + l] = rotl32(w, 24);
+        if (DEC) sm[32768 + i * 64 + l] = (uint32_t)c_inv_sbox[i] * 0x01010101u;
+    }
+}
+
+/* lookup address: byte K of x -> address byte 1, lane*4 -> address byte 0 */
+template <int K>
+__device__ __forceinline__ uint32_t baddr(uint32_t x, uint32_t lane4)
+{
+    return __byte_perm(x, lane4, 0x5504 | (K << 4));
+}
+
+template <int OFF>
+__device__ __forceinline__ uint32_t lds32(uint32_t addr)
+{
+    uint32_t v;
+    asm("ld.shared.u32 %0, [%1+%2];" : "=r"(v) : "r"(addr), "n"(OFF));
+    return v;
+}
+
+/* Shared-memory context of a thread: `base` is the shared-window address of
+ * the tables (a ptxas-time constant, it folds into the LDS immediate together
+ * with the table offset); `lane4` = lane*4 selects the thread's bank. */
+struct Tb { uint32_t base, lane4; };
+
+/* TB(OFF, K, x): table at byte offset OFF, indexed by byte K of x — one PRMT + one LDS */
+#define TB(OFF, K, x) lds32<OFF>(tb.base + baddr<K>((x), tb.lane4))
+
+struct State { uint32_t a, b, c, d; };
+
+/* one forward table round, AES_FROUND (aes.c:601-622) */
+__device__ __forceinline__ State enc_round(const State s, const uint32_t *rk, const Tb tb)
+{
+    State t;
+    t.a = TB(OFF_T0, 0, s.a) ^ TB(OFF_T1, 1, s.b) ^ TB(OFF_T2, 2, s.c) ^ TB(OFF_T3, 3, s.d) ^ rk[0];
+    t.b = TB(OFF_T0, 0, s.b) ^ TB(OFF_T1, 1, s.c) ^ TB(OFF_T2, 2, s.d) ^ TB(OFF_T3, 3, s.a) ^ rk[1];
+    t.c = TB(OFF_T0, 0, s.c) ^ TB(OFF_T1, 1, s.d) ^ TB(OFF_T2, 2, s.a) ^ TB(OFF_T3, 3, s.b) ^ rk[2];
+    t.d = TB(OFF_T0, 0, s.d) ^ TB(OFF_T1, 1, s.a) ^ TB(OFF_T2, 2, s.b) ^ TB(OFF_T3, 3, s.c) ^ rk[3];
+    return t;
+}
+
+/* one reverse table round, AES_RROUND (aes.c:624-645) */
+__device__ __forceinline__ State dec_round(const State s, const uint32_t *rk, const Tb tb)
+{
+    State t;
+    t.a = TB(OFF_T0, 0, s.a) ^ TB(OFF_T1, 1, s.d) ^ TB(OFF_T2, 2, s.c) ^ TB(OFF_T3, 3, s.b) ^ rk[0];
+    t.b = TB(OFF_T0, 0, s.b) ^ TB(OFF_T1, 1, s.a) ^ TB(OFF_T2, 2, s.d) ^ TB(OFF_T3, 3, s.c) ^ rk[1];
+    t.c = TB(OFF_T0, 0, s.c) ^ TB(OFF_T1, 1, s.b) ^ TB(OFF_T2, 2, s.a) ^ TB(OFF_T3, 3, s.d) ^ rk[2];
+    t.d = TB(OFF_T0, 0, s.d) ^ TB(OFF_T1, 1, s.c) ^ TB(OFF_T2, 2, s.b) ^ TB(OFF_T3, 3, s.a) ^ rk[3];
+    return t;
+}
+
+/* pick byte0 of w0, byte1 of w1, byte2 of w2, byte3 of w3 */
+__device__ __forceinline__ uint32_t merge_bytes(uint32_t w0, uint32_t w1, uint32_t w2, uint32_t w3)
+{
+    return __byte_perm(__byte_perm(w0, w1, 0x0050), __byte_perm(w2, w3, 0x7200), 0x7610);
+}
+
+/* Last forward round (aes.c:721-743).  Plain S(x) is read out of the T-tables:
+ * byte 0 of FT2, byte 1 of FT3, byte 2 of FT0, byte 3 of FT1 are all S(x). */
+__device__ __forceinline__ State enc_last(const State s, const uint32_t *rk, const Tb tb)
+{
+    State t;
+    t.a = merge_bytes(TB(OFF_T2, 0, s.a), TB(OFF_T3, 1, s.b), TB(OFF_T0, 2, s.c), TB(OFF_T1, 3, s.d)) ^ rk[0];
+    t.b = merge_bytes(TB(OFF_T2, 0, s.b), TB(OFF_T3, 1, s.c), TB(OFF_T0, 2, s.d), TB(OFF_T1, 3, s.a)) ^ rk[1];
+    t.c = merge_bytes(TB(OFF_T2, 0, s.c), TB(OFF_T3, 1, s.d), TB(OFF_T0, 2, s.a), TB(OFF_T1, 3, s.b)) ^ rk[2];
+    t.d = merge_bytes(TB(OFF_T2, 0, s.d), TB(OFF_T3, 1, s.a), TB(OFF_T0, 2, s.b), TB(OFF_T1, 3, s.c)) ^ rk[3];
+    return t;
+}
+
+/* Last reverse round (aes.c:687-709) from the byte-replicated RSb table. */
+__device__ __forceinline__ State dec_last(const State s, const uint32_t *rk, const Tb tb)
+{
+    State t;
+    t.a = merge_bytes(TB(OFF_SB, 0, s.a), TB(OFF_SB, 1, s.d), TB(OFF_SB, 2, s.c), TB(OFF_SB, 3, s.b)) ^ rk[0];
+    t.b = merge_bytes(TB(OFF_SB, 0, s.b), TB(OFF_SB, 1, s.a), TB(OFF_SB, 2, s.d), TB(OFF_SB, 3, s.c)) ^ rk[1];
+    t.c = merge_bytes(TB(OFF_SB, 0, s.c), TB(OFF_SB, 1, s.b), TB(OFF_SB, 2, s.a), TB(OFF_SB, 3, s.d)) ^ rk[2];
+    t.d = merge_bytes(TB(OFF_SB, 0, s.d), TB(OFF_SB, 1, s.c), TB(OFF_SB, 2, s.b), TB(OFF_SB, 3, s.a)) ^ rk[3];
+    return t;
+}
+
+template <int NR, bool DEC>
+__device__ __forceinline__ State cipher_block(State s, const AesSched &ks, const Tb tb)
+{
+    s.a ^= ks.rk[0]; s.b ^= ks.rk[1]; s.c ^= ks.rk[2]; s.d ^= ks.rk[3];
+#pragma unroll
+    for (int r = 1; r < NR; r++) s = DEC ? dec_round(s, ks.rk + 4 * r, tb) : enc_round(s, ks.rk + 4 * r, tb);
+    return DEC ? dec_last(s, ks.rk + 4 * NR, tb) : enc_last(s, ks.rk + 4 * NR, tb);
+}
+
+__device__ __forceinline__ uint32_t smem_base_u32(const void *p)
+{
+    return (uint32_t)__cvta_generic_to_shared(p);
+}
+
+__device__ __forceinline__ uint4 ld_stream(const uint4 *p) { return __ldcs(p); }
+__device__ __forceinline__ void  st_stream(uint4 *p, uint4 v) { __stcs(p, v); }
+
+/* ------------------------------------------------------------------- CTR */
+
+struct CtrArgs {
+    uint64_t base_hi, base_lo;   /* counter of virtual block 0 (low byte of base_lo is 0) */
+    uint32_t c_lo;               /* low byte of the first real counter: virtual index of block 0 */
+    uint32_t carry128;           /* 1: carry from bytes 8..15 into 0..7 (aes.c:884-888); 0: aesni.c:139 */
+    const uint4 *in;
+    uint4 *out;
+    uint64_t nblocks;            /* whole 16-byte blocks */
+    uint32_t tail;               /* bytes of a final partial block, 0..15 */
+    uint64_t n_chunks;
+    uint4 *last_ks;              /* optional: keystream of the last block touched */
+};
+
+template <int NR>
+__global__ void __launch_bounds__(kThreads, 1)
+aes_ctr_kernel(const __grid_constant__ AesSched ks, const __grid_constant__ CtrArgs a)
+{
+    extern __shared__ __align__(1024) uint32_t smem[];
+    fill_tables<false>(smem);
+    __syncthreads();
+
+    const uint32_t lane = threadIdx.x & 31u;
+    Tb tb = { smem_base_u32(smem), lane * 4u };
+    asm volatile("" : "+r"(tb.lane4));    /* pin table reads below the barrier */
+
+    const uint32_t k3 = ks.rk[3] >> 24;
+    /* address of FT3[(j ^ k3)] for j = lane; row `it` flips bits of j above bit 4 */
+    const uint32_t a3_lane = (((lane ^ k3) & 0xffu) << 8) | tb.lane4;
+    const uint64_t nb_all = a.nblocks + (a.tail ? 1u : 0u);
+    const uint64_t warp_gid = (uint64_t)blockIdx.x * kWarps + (threadIdx.x >> 5);
+    const uint64_t n_warps = (uint64_t)gridDim.x * kWarps;
+
+    for (uint64_t chunk = warp_gid; chunk < a.n_chunks; chunk += n_warps) {
+        /* ---- per-group constants: lane i works on group chunk*8 + (i & 7) ---- */
+        uint32_t C0, D0, D1, D2, D3;
+        {
+            const uint64_t g = chunk * kGroupsPerChunk + (lane & (kGroupsPerChunk - 1));
+            const uint64_t lo = a.base_lo + (g << 8);
+            const uint64_t hi = a.base_hi + ((a.carry128 && lo < a.base_lo) ? 1u : 0u);
+            const uint32_t s0 = __byte_perm((uint32_t)(hi >> 32), 0, 0x0123) ^ ks.rk[0];
+            const uint32_t s1 = __byte_perm((uint32_t)hi, 0, 0x0123) ^ ks.rk[1];
+            const uint32_t s2 = __byte_perm((uint32_t)(lo >> 32), 0, 0x0123) ^ ks.rk[2];
+            const uint32_t s3 = __byte_perm((uint32_t)lo, 0, 0x0123) ^ ks.rk[3];   /* byte 3 varies per block */
+            C0 = TB(OFF_T0, 0, s0) ^ TB(OFF_T1, 1, s1) ^ TB(OFF_T2, 2, s2) ^ ks.rk[4];
+            const uint32_t X1 = TB(OFF_T0, 0, s1) ^ TB(OFF_T1, 1, s2) ^ TB(OFF_T2, 2, s3) ^ TB(OFF_T3, 3, s0) ^ ks.rk[5];
+            const uint32_t X2 = TB(OFF_T0, 0, s2) ^ TB(OFF_T1, 1, s3) ^ TB(OFF_T2, 2, s0) ^ TB(OFF_T3, 3, s1) ^ ks.rk[6];
+            const uint32_t X3 = TB(OFF_T0, 0, s3) ^ TB(OFF_T1, 1, s0) ^ TB(OFF_T2, 2, s1) ^ TB(OFF_T3, 3, s2) ^ ks.rk[7];
+            D0 = TB(OFF_T1, 1, X1) ^ TB(OFF_T2, 2, X2) ^ TB(OFF_T3, 3, X3) ^ ks.rk[8];
+            D1 = TB(OFF_T0, 0, X1) ^ TB(OFF_T1, 1, X2) ^ TB(OFF_T2, 2, X3) ^ ks.rk[9];
+            D2 = TB(OFF_T0, 0, X2) ^ TB(OFF_T1, 1, X3) ^ TB(OFF_T3, 3, X1) ^ ks.rk[10];
+            D3 = TB(OFF_T0, 0, X3) ^ TB(OFF_T2, 2, X1) ^ TB(OFF_T3, 3, X2) ^ ks.rk[11];
+        }
+
+        const uint64_t v0 = chunk * (uint64_t)(kGroupsPerChunk * 256);   /* first virtual index */
+        const bool full = (v0 >= a.c_lo) && (v0 + kGroupsPerChunk * 256 <= a.c_lo + a.nblocks);
+
+#pragma unroll 1
+        for (int gi = 0; gi < kGroupsPerChunk; gi++) {
+            const uint32_t c0 = __shfl_sync(0xffffffffu, C0, gi);
+            const uint32_t d0 = __shfl_sync(0xffffffffu, D0, gi);
+            const uint32_t d1 = __shfl_sync(0xffffffffu, D1, gi);
+            const uint32_t d2 = __shfl_sync(0xffffffffu, D2, gi);
+            const uint32_t d3 = __shfl_sync(0xffffffffu, D3, gi);
+            const uint64_t vg = v0 + (uint64_t)gi * 256 + lane;          /* this lane's row-0 virtual index */
+
+#pragma unroll 2
+            for (int it = 0; it < kRowsPerGroup; it++) {
+                /* rounds 1-2 with the cached constants: 5 lookups instead of 32 */
+                const uint32_t x0 = c0 ^ lds32<OFF_T3>(tb.base + (a3_lane ^ ((uint32_t)it << 13)));
+                State s;
+                s.a = d0 ^ TB(OFF_T0, 0, x0);
+                s.b = d1 ^ TB(OFF_T3, 3, x0);
+                s.c = d2 ^ TB(OFF_T2, 2, x0);
+                s.d = d3 ^ TB(OFF_T1, 1, x0);
+#pragma unroll
+                for (int r = 3; r < NR; r++) s = enc_round(s, ks.rk + 4 * r, tb);
+                s = enc_last(s, ks.rk + 4 * NR, tb);
+
+                const uint64_t v = vg + (uint64_t)it * 32;
+                const uint64_t b = v - a.c_lo;
+                if (full) {
+                    uint4 p = ld_stream(a.in + b);
+                    p.x ^= s.a; p.y ^= s.b; p.z ^= s.c; p.w ^= s.d;
+                    st_stream(a.out + b, p);
+                } else if (v >= a.c_lo && b < nb_all) {
+                    if (b < a.nblocks) {
+                        uint4 p = ld_stream(a.in + b);
+                        p.x ^= s.a; p.y ^= s.b; p.z ^= s.c; p.w ^= s.d;
+                        st_stream(a.out + b, p);
+                    } else {                                   /* ragged tail, byte-wise (aes.c:879-895) */
+                        const unsigned char *pi = (const unsigned char *)(a.in + b);
+                        unsigned char *po = (unsigned char *)(a.out + b);
+                        for (uint32_t i = 0; i < a.tail; i++) {
+                            const uint32_t q = i >> 2;
+                            const uint32_t w = q == 0 ? s.a : q == 1 ? s.b : q == 2 ? s.c : s.d;
+                            po[i] = pi[i] ^ (unsigned char)(w >> (8 * (i & 3)));
+                        }
+                    }
+                    if (a.last_ks && b == nb_all - 1) *a.last_ks = make_uint4(s.a, s.b, s.c, s.d);
+                }
+            }
+        }
+    }
+}
+
+/* --------------------------------------------------- ECB enc/dec, CBC dec */
+
+enum { MODE_ECB_ENC = 0, MODE_ECB_DEC = 1, MODE_CBC_DEC = 2 };
+
+struct BlkArgs {
+    const uint4 *in;
+    uint4 *out;
+    uint64_t nblocks;
+    uint64_t n_groups;       /* ceil(nblocks / 256) */
+    uint4 iv;                /* CBC: block before block 0 */
+    const uint4 *boundary;   /* CBC in-place: boundary[g] = ciphertext block 256*g - 1 (g >= 1) */
+};
+
+template <int NR, int MODE>
+__global__ void __launch_bounds__(kThreads, 1)
+aes_blocks_kernel(const __grid_constant__ AesSched ks, const __grid_constant__ BlkArgs a)
+{
+    constexpr bool DEC = (MODE != MODE_ECB_ENC);
+    extern __shared__ __align__(1024) uint32_t smem[];
+    fill_tables<DEC>(smem);
+    __syncthreads();
+
+    const uint32_t lane = threadIdx.x & 31u;
+    Tb tb = { smem_base_u32(smem), lane * 4u };
+    asm volatile("" : "+r"(tb.lane4));
+
+    const uint64_t warp_gid = (uint64_t)blockIdx.x * kWarps + (threadIdx.x >> 5);
+    const uint64_t n_warps = (uint64_t)gridDim.x * kWarps;
+
+    for (uint64_t g = warp_gid; g < a.n_groups; g += n_warps) {
+        const uint64_t b0 = g * 256 + lane;
+        const bool full = (g * 256 + 256 <= a.nblocks);
+        uint4 carry = make_uint4(0, 0, 0, 0);      /* CBC: lane 31's ciphertext of the previous row */
+        if (MODE == MODE_CBC_DEC) {
+            if (g == 0) carry = a.iv;
+            else carry = a.boundary ? a.boundary[g] : a.in[g * 256 - 1];
+        }
+#pragma unroll 2
+        for (int it = 0; it < kRowsPerGroup; it++) {
+            const uint64_t b = b0 + (uint64_t)it * 32;
+            const bool live = full || b < a.nblocks;
+            uint4 c = make_uint4(0, 0, 0, 0);
+            if (live) c = ld_stream(a.in + b);
+            State s = { c.x, c.y, c.z, c.w };
+            s = cipher_block<NR, DEC>(s, ks, tb);
+            if (MODE == MODE_CBC_DEC) {            /* P_i = D(C_i) ^ C_{i-1}  (aes.c:784-797) */
+                uint4 prev;
+                prev.x = __shfl_up_sync(0xffffffffu, c.x, 1);
+                prev.y = __shfl_up_sync(0xffffffffu, c.y, 1);
+                prev.z = __shfl_up_sync(0xffffffffu, c.z, 1);
+                prev.w = __shfl_up_sync(0xffffffffu, c.w, 1);
+                if (lane == 0) prev = carry;
+                carry.x = __shfl_sync(0xffffffffu, c.x, 31);
+                carry.y = __shfl_sync(0xffffffffu, c.y, 31);
+                carry.z = __shfl_sync(0xffffffffu, c.z, 31);
+                carry.w = __shfl_sync(0xffffffffu, c.w, 31);
+                s.a ^= prev.x; s.b ^= prev.y; s.c ^= prev.z; s.d ^= prev.w;
+            }
+            if (live) st_stream(a.out + b, make_uint4(s.a, s.b, s.c, s.d));
+        }
+    }
+}
+
+/* CBC in-place pre-pass: save the ciphertext block in front of every 256-block
+ * group before the main kernel overwrites it. */
+__global__ void cbc_save_boundaries_kernel(const uint4 *in, uint4 *boundary, uint64_t n_groups)
+{
+    uint64_t g = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (g >= 1 && g < n_groups) boundary[g] = in[g * 256 - 1];
+}
+
+/* ------------------------------------------- CBC encrypt, batched messages */
+
+struct CbcEncArgs {
+    const uint4 *in;
+    uint4 *out;
+    const uint4 *ivs;
+    uint4 *ivs_out;
+    uint64_t n_msgs;
+    uint64_t blocks_per_msg;
+};
+
+/* One thread per message: the chain C_i = E(P_i ^ C_{i-1}) (aes.c:801-812) is
+ * serial inside a message and independent across messages. */
+template <int NR>
+__global__ void __launch_bounds__(kThreads, 1)
+aes_cbc_enc_batch_kernel(const __grid_constant__ AesSched ks, const __grid_constant__ CbcEncArgs a)
+{
+    extern __shared__ __align__(1024) uint32_t smem[];
+    fill_tables<false>(smem);
+    __syncthreads();
+    const uint32_t lane = threadIdx.x & 31u;
+    Tb tb = { smem_base_u32(smem), lane * 4u };
+    asm volatile("" : "+r"(tb.lane4));
+
+    const uint64_t n_threads = (uint64_t)gridDim.x * blockDim.x;
+    for (uint64_t m = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x; m < a.n_msgs; m += n_threads) {
+        uint4 c = a.ivs[m];
+        const uint4 *pi = a.in + m * a.blocks_per_msg;
+        uint4 *po = a.out + m * a.blocks_per_msg;
+        /* two blocks (one 32-byte sector) per trip; the load of the next pair is independent of the chain */
+        uint64_t i = 0;
+        for (; i + 2 <= a.blocks_per_msg; i += 2) {
+            const uint4 p0 = pi[i], p1 = pi[i + 1];
+            State s = { p0.x ^ c.x, p0.y ^ c.y, p0.z ^ c.z, p0.w ^ c.w };
+            s = cipher_block<NR, false>(s, ks, tb);
+            const uint4 c0 = make_uint4(s.a, s.b, s.c, s.d);
+            State t = { p1.x ^ c0.x, p1.y ^ c0.y, p1.z ^ c0.z, p1.w ^ c0.w };
+            t = cipher_block<NR, false>(t, ks, tb);
+            c = make_uint4(t.a, t.b, t.c, t.d);
+            po[i] = c0;
+            po[i + 1] = c;
+        }
+        if (i < a.blocks_per_msg) {
+            const uint4 p0 = pi[i];
+            State s = { p0.x ^ c.x, p0.y ^ c.y, p0.z ^ c.z, p0.w ^ c.w };
+            s = cipher_block<NR, false>(s, ks, tb);
+            c = make_uint4(s.a, s.b, s.c, s.d);
+            po[i] = c;
+        }
+        if (a.ivs_out) a.ivs_out[m] = c;     /* iv <- last ciphertext block (aes.c:807) */
+    }
+}
+
+/* ------------------------------------------------------------ host helpers */
+
+int check_common(const uint32_t *rk, int nr, const void *in, const void *out, size_t nbytes)
+{
+    if (!rk || (nr != 10 && nr != 12 && nr != 14)) {
+        bc_set_error("bad key schedule (rk=%p, nr=%d; nr must be 10, 12 or 14)", (const void *)rk, nr);
+        return BC_ERR_BAD_ARG;
+    }
+    if (nbytes && (!in || !out)) {
+        bc_set_error("NULL data pointer with nbytes=%zu", nbytes);
+        return BC_ERR_BAD_ARG;
+    }
+    if (((uintptr_t)in | (uintptr_t)out) & 15u) {
+        bc_set_error("device buffers must be 16-byte aligned");
+        return BC_ERR_BAD_ARG;
+    }
+    return BC_OK;
+}
+
+int check_overlap(const void *in, const void *out, size_t nbytes)
+{
+    const uintptr_t i = (uintptr_t)in, o = (uintptr_t)out;
+    if (i != o && i < o + nbytes && o < i + nbytes) {
+        bc_set_error("input and output overlap partially; they must be identical or disjoint");
+        return BC_ERR_OVERLAP;
+    }
+    return BC_OK;
+}
+
+void load_sched(AesSched &ks, const uint32_t *rk, int nr)
+{
+    for (int i = 0; i < 60; i++) ks.rk[i] = (i < 4 * (nr + 1)) ? rk[i] : 0u;
+}
+
+template <typename K>
+int set_smem(K kernel, int bytes)
+{
+    BC_CUDA(cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, bytes),
+            "cudaFuncSetAttribute(MaxDynamicSharedMemorySize)");
+    return BC_OK;
+}
+
+int grid_for(uint64_t warp_items)
+{
+    int sms = bc_cached_sm_count();
+    if (sms <= 0) return -1;
+    uint64_t ctas = (warp_items + kWarps - 1) / kWarps;
+    if (ctas < 1) ctas = 1;
+    return (int)(ctas < (uint64_t)sms ? ctas : (uint64_t)sms);
+}
+
+template <int NR>
+int launch_ctr(const AesSched &ks, const CtrArgs &a, cudaStream_t st)
+{
+    int rc = set_smem(aes_ctr_kernel<NR>, kEncSmemBytes);
+    if (rc) return rc;
+    int grid = grid_for(a.n_chunks);
+    if (grid < 0) return BC_ERR_CUDA;
+    aes_ctr_kernel<NR><<<grid, kThreads, kEncSmemBytes, st>>>(ks, a);
+    BC_CUDA(cudaGetLastError(), "aes_ctr_kernel launch");
+    return BC_OK;
+}
+
+template <int NR, int MODE>
+int launch_blocks(const AesSched &ks, const BlkArgs &a, cudaStream_t st)
+{
+    constexpr int smem = (MODE == MODE_ECB_ENC) ? kEncSmemBytes : kDecSmemBytes;
+    int rc = set_smem(aes_blocks_kernel<NR, MODE>, smem);
+    if (rc) return rc;
+    int grid = grid_for(a.n_groups);
+    if (grid < 0) return BC_ERR_CUDA;
+    aes_blocks_kernel<NR, MODE><<<grid, kThreads, smem, st>>>(ks, a);
+    BC_CUDA(cudaGetLastError(), "aes_blocks_kernel launch");
+    return BC_OK;
+}
+
+template <int MODE>
+int launch_blocks_nr(int nr, const AesSched &ks, const BlkArgs &a, cudaStream_t st)
+{
+    switch (nr) {
+    case 10: return launch_blocks<10, MODE>(ks, a, st);
+    case 12: return launch_blocks<12, MODE>(ks, a, st);
+    default: return launch_blocks<14, MODE>(ks, a, st);
+    }
+}
+
+template <int NR>
+int launch_cbc_enc(const AesSched &ks, const CbcEncArgs &a, cudaStream_t st)
+{
+    int rc = set_smem(aes_cbc_enc_batch_kernel<NR>, kEncSmemBytes);
+    if (rc) return rc;
+    int sms = bc_cached_sm_count();
+    if (sms <= 0) return BC_ERR_CUDA;
+    /* spread the messages evenly: ceil(n/SMs) threads per CTA, whole warps, <= 512 */
+    uint64_t per = (a.n_msgs + sms - 1) / sms;
+    per = ((per + 31) / 32) * 32;
+    if (per > kThreads) per = kThreads;
+    uint64_t ctas = (a.n_msgs + per - 1) / per;
+    int grid = (int)(ctas < (uint64_t)sms ? ctas : (uint64_t)sms);
+    aes_cbc_enc_batch_kernel<NR><<<grid, (int)per, kEncSmemBytes, st>>>(ks, a);
+    BC_CUDA(cudaGetLastError(), "aes_cbc_enc_batch_kernel launch");
+    return BC_OK;
+}
+
+}  // namespace
+
+/* ------------------------------------------------------------- C-ABI (dev) */
+
+extern "C" int bc_aes_ctr_dev(const uint32_t *rk, int nr, const unsigned char counter[16], int counter_bits,
+                              uint64_t first_block, const void *d_in, void *d_out, size_t nbytes,
+                              void *d_last_keystream, void *stream)
+{
+    int rc = check_common(rk, nr, d_in, d_out, nbytes);
+    if (rc) return rc;
+    if (!counter || (counter_bits != 128 && counter_bits != 64)) {
+        bc_set_error("counter must be non-NULL and counter_bits 64 or 128 (got %d)", counter_bits);
+        return BC_ERR_BAD_ARG;
+    }
+    if ((rc = check_overlap(d_in, d_out, nbytes))) return rc;
+    if (nbytes == 0) return BC_OK;
+
+    uint64_t hi = 0, lo = 0;
+    for (int i = 0; i < 8; i++) { hi = (hi << 8) | counter[i]; lo = (lo << 8) | counter[8 + i]; }
+    const uint64_t lo2 = lo + first_block;
+    if (counter_bits == 128 && lo2 < lo) hi++;
+
+    AesSched ks;
+    load_sched(ks, rk, nr);
+    CtrArgs a;
+    a.c_lo = (uint32_t)(lo2 & 0xffu);
+    a.base_lo = lo2 & ~(uint64_t)0xffu;
+    a.base_hi = hi;
+    a.carry128 = (counter_bits == 128);
+    a.in = (const uint4 *)d_in;
+    a.out = (uint4 *)d_out;
+    a.nblocks = nbytes / 16;
+    a.tail = (uint32_t)(nbytes % 16);
+    const uint64_t nb_all = a.nblocks + (a.tail ? 1 : 0);
+    const uint64_t per_chunk = (uint64_t)kGroupsPerChunk * 256;
+    a.n_chunks = (a.c_lo + nb_all + per_chunk - 1) / per_chunk;
+    a.last_ks = (uint4 *)d_last_keystream;
+    cudaStream_t st = (cudaStream_t)stream;
+    switch (nr) {
+    case 10: return launch_ctr<10>(ks, a, st);
+    case 12: return launch_ctr<12>(ks, a, st);
+    default: return launch_ctr<14>(ks, a, st);
+    }
+}
+
+extern "C" int bc_aes_ecb_dev(const uint32_t *rk, int nr, int mode, const void *d_in, void *d_out,
+                              size_t nbytes, void *stream)
+{
+    int rc = check_common(rk, nr, d_in, d_out, nbytes);
+    if (rc) return rc;
+    if (mode != BC_ENCRYPT && mode != BC_DECRYPT) {
+        bc_set_error("mode must be BC_ENCRYPT (1) or BC_DECRYPT (0), got %d", mode);
+        return BC_ERR_BAD_ARG;
+    }
+    if ((rc = check_overlap(d_in, d_out, nbytes))) return rc;
+    AesSched ks;
+    load_sched(ks, rk, nr);
+    BlkArgs a = {};
+    a.in = (const uint4 *)d_in;
+    a.out = (uint4 *)d_out;
+    a.nblocks = nbytes / 16;            /* whole blocks only, like the harness loop */
+    a.n_groups = (a.nblocks + 255) / 256;
+    if (a.nblocks == 0) return BC_OK;
+    cudaStream_t st = (cudaStream_t)stream;
+    return mode == BC_ENCRYPT ? launch_blocks_nr<MODE_ECB_ENC>(nr, ks, a, st)
+                              : launch_blocks_nr<MODE_ECB_DEC>(nr, ks, a, st);
+}
+
+extern "C" int bc_aes_cbc_decrypt_dev(const uint32_t *rk, int nr, const unsigned char iv[16],
+                                      const void *d_in, void *d_out, size_t nbytes, void *stream)
+{
+    int rc = check_common(rk, nr, d_in, d_out, nbytes);
+    if (rc) return rc;
+    if (!iv) { bc_set_error("iv is NULL"); return BC_ERR_BAD_ARG; }
+    if (nbytes % 16) { bc_set_error("CBC length %zu is not a multiple of 16", nbytes); return BC_ERR_BAD_ARG; }
+    if ((rc = check_overlap(d_in, d_out, nbytes))) return rc;
+    if (nbytes == 0) return BC_OK;
+    AesSched ks;
+    load_sched(ks, rk, nr);
+    BlkArgs a = {};
+    a.in = (const uint4 *)d_in;
+    a.out = (uint4 *)d_out;
+    a.nblocks = nbytes / 16;
+    a.n_groups = (a.nblocks + 255) / 256;
+    uint32_t w[4];
+    for (int i = 0; i < 4; i++)
+        w[i] = (uint32_t)iv[4 * i] | ((uint32_t)iv[4 * i + 1] << 8) | ((uint32_t)iv[4 * i + 2] << 16) |
+               ((uint32_t)iv[4 * i + 3] << 24);
+    a.iv = make_uint4(w[0], w[1], w[2], w[3]);
+    cudaStream_t st = (cudaStream_t)stream;
+    if (d_in == d_out && a.n_groups > 1) {
+        /* in place: the block in front of each group would be overwritten by a
+         * neighbouring warp — keep copies in library-owned scratch first */
+        void *scratch = nullptr;
+        if ((rc = bc_scratch_get((void *)st, a.n_groups * sizeof(uint4), &scratch))) return rc;
+        const int tpb = 256;
+        const unsigned blocks = (unsigned)((a.n_groups + tpb - 1) / tpb);
+        cbc_save_boundaries_kernel<<<blocks, tpb, 0, st>>>(a.in, (uint4 *)scratch, a.n_groups);
+        BC_CUDA(cudaGetLastError(), "cbc_save_boundaries_kernel launch");
+        a.boundary = (const uint4 *)scratch;
+    }
+    return launch_blocks_nr<MODE_CBC_DEC>(nr, ks, a, st);
+}
+
+extern "C" int bc_aes_cbc_encrypt_batch_dev(const uint32_t *rk, int nr, size_t n_msgs, size_t msg_len,
+                                            const void *d_ivs, void *d_ivs_out,
+                                            const void *d_in, void *d_out, void *stream)
+{
+    int rc = check_common(rk, nr, d_in, d_out, n_msgs * msg_len);
+    if (rc) return rc;
+    if (msg_len % 16) { bc_set_error("CBC message length %zu is not a multiple of 16", msg_len); return BC_ERR_BAD_ARG; }
+    if (n_msgs == 0 || msg_len == 0) return BC_OK;
+    if (!d_ivs || ((uintptr_t)d_ivs & 15u) || ((uintptr_t)d_ivs_out & 15u)) {
+        bc_set_error("d_ivs must be non-NULL and 16-byte aligned");
+        return BC_ERR_BAD_ARG;
+    }
+    if ((rc = check_overlap(d_in, d_out, n_msgs * msg_len))) return rc;
+    AesSched ks;
+    load_sched(ks, rk, nr);
+    CbcEncArgs a;
+    a.in = (const uint4 *)d_in;
+    a.out = (uint4 *)d_out;
+    a.ivs = (const uint4 *)d_ivs;
+    a.ivs_out = (uint4 *)d_ivs_out;
+    a.n_msgs = n_msgs;
+    a.blocks_per_msg = msg_len / 16;
+    cudaStream_t st = (cudaStream_t)stream;
+    switch (nr) {
+    case 10: return launch_cbc_enc<10>(ks, a, st);
+    case 12: return launch_cbc_enc<12>(ks, a, st);
+    default: return launch_cbc_enc<14>(ks, a, st);
+    }
+}

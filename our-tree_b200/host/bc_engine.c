@@ -1,0 +1,717 @@
+/*
+ * bc_engine.c — host side of libbulkcipher.so, in C: per-thread error slot,
+ * device bookkeeping, library-owned scratch, and the HOST-buffer entry points
+ * (bc_*_host): a chunked, multi-stream H2D -> kernel -> D2H pipeline around the
+ * device entry points of csrc/.  This is the layer the reference's drop-in
+ * symbols (aes_dropin.c, aesni_dropin.c, arc4_dropin.c, rc4_dropin.c) call.
+ *
+ * The reference has no counterpart for most of this: its only device boundary
+ * is cudaMalloc + cudaMemcpy + launch + cudaMemcpy + cudaFree per call, all
+ * unchecked and serial (aes-gpu/Source/AES.cu:230-255).  Here every CUDA call
+ * is checked, buffers persist per device, and copies overlap compute.
+ *
+ * There is no CPU fallback: if CUDA is unusable every entry point fails.
+ */
+#include <pthread.h>
+#include <stdarg.h>
+#include <stdio.h>
+#include <stdlib.h>
+#include <string.h>
+
+#include <cuda_runtime_api.h>
+
+#include "bulkcipher.h"
+#include "../csrc/bc_internal.h"
+
+#define BC_MAX_DEVICES 16
+#define BC_SLOTS       3
+#define BC_CHUNK_BYTES ((size_t)32 << 20)   /* pipeline granule; a multiple of 4 KiB */
+#define BC_MAX_SCRATCH 8
+
+/* ------------------------------------------------------------ error slot */
+
+static __thread char tls_error[512];
+static __thread int  tls_device = 0;
+
+void bc_set_error(const char *fmt, ...)
+{
+    va_list ap;
+    va_start(ap, fmt);
+    vsnprintf(tls_error, sizeof tls_error, fmt, ap);
+    va_end(ap);
+}
+
+int bc_cuda_fail(int cuda_err, const char *what)
+{
+    bc_set_error("%s: %s (%s)", what, cudaGetErrorString((cudaError_t)cuda_err),
+                 cudaGetErrorName((cudaError_t)cuda_err));
+    return BC_ERR_CUDA;
+}
+
+const char *bc_last_error(void) { return tls_error; }
+
+/* ---------------------------------------------------------- device state */
+
+typedef struct {
+    cudaStream_t stream;
+    cudaEvent_t  done;
+    unsigned char *d_buf;       /* BC_CHUNK_BYTES of HBM, processed in place */
+    unsigned char *pin_in;      /* staging for pageable callers (lazy) */
+    unsigned char *pin_out;
+    /* pending copy-out of a staged chunk */
+    unsigned char *pend_dst;
+    size_t         pend_len;
+} bc_slot;
+
+typedef struct {
+    void *key;                  /* stream the buffer was last handed out for */
+    void *ptr;
+    size_t cap;
+} bc_scratch;
+
+typedef struct {
+    pthread_mutex_t lock;       /* one host-pipeline call at a time per device */
+    pthread_mutex_t scratch_lock;
+    int        ready;
+    int        sm_count;
+    bc_slot    slot[BC_SLOTS];
+    bc_scratch scratch[BC_MAX_SCRATCH];
+    unsigned char *d_aux;       /* small device buffer: ivs, keys, contexts, last keystream */
+    size_t     aux_cap;
+} bc_dev;
+
+static bc_dev g_dev[BC_MAX_DEVICES];
+static pthread_once_t g_once = PTHREAD_ONCE_INIT;
+
+static void init_locks(void)
+{
+    for (int i = 0; i < BC_MAX_DEVICES; i++) {
+        pthread_mutex_init(&g_dev[i].lock, NULL);
+        pthread_mutex_init(&g_dev[i].scratch_lock, NULL);
+    }
+}
+
+int bc_device_count(void)
+{
+    int n = 0;
+    cudaError_t e = cudaGetDeviceCount(&n);
+    if (e != cudaSuccess) { bc_cuda_fail((int)e, "cudaGetDeviceCount"); return 0; }
+    return n;
+}
+
+int bc_set_device(int device)
+{
+    int n = bc_device_count();
+    if (n <= 0) { if (!tls_error[0]) bc_set_error("no CUDA device"); return BC_ERR_NO_DEVICE; }
+    if (device < 0 || device >= n || device >= BC_MAX_DEVICES) {
+        bc_set_error("device %d out of range (have %d)", device, n);
+        return BC_ERR_BAD_ARG;
+    }
+    BC_CUDA(cudaSetDevice(device), "cudaSetDevice");
+    tls_device = device;
+    return BC_OK;
+}
+
+int bc_get_device(void) { return tls_device; }
+
+static bc_dev *cur_dev_state(int *dev_out)
+{
+    int dev = 0;
+    pthread_once(&g_once, init_locks);
+    if (cudaGetDevice(&dev) != cudaSuccess || dev < 0 || dev >= BC_MAX_DEVICES) return NULL;
+    if (dev_out) *dev_out = dev;
+    return &g_dev[dev];
+}
+
+int bc_cached_sm_count(void)
+{
+    int dev = 0;
+    bc_dev *d = cur_dev_state(&dev);
+    if (!d) { bc_set_error("no current CUDA device"); return -1; }
+    if (d->sm_count <= 0) {
+        int n = 0;
+        cudaError_t e = cudaDeviceGetAttribute(&n, cudaDevAttrMultiProcessorCount, dev);
+        if (e != cudaSuccess) { bc_cuda_fail((int)e, "cudaDeviceGetAttribute(SM count)"); return -1; }
+        d->sm_count = n;
+    }
+    return d->sm_count;
+}
+
+int bc_sm_count(void)
+{
+    if (bc_set_device(tls_device)) return -1;
+    return bc_cached_sm_count();
+}
+
+/* Scratch in HBM, grow-only, one buffer per stream key so calls on different
+ * streams do not share it.  Calls that reuse a stream are ordered by the
+ * stream itself. */
+int bc_scratch_get(void *key, size_t bytes, void **d_ptr)
+{
+    bc_dev *d = cur_dev_state(NULL);
+    if (!d) { bc_set_error("no current CUDA device"); return BC_ERR_NO_DEVICE; }
+    pthread_mutex_lock(&d->scratch_lock);
+    bc_scratch *s = NULL;
+    for (int i = 0; i < BC_MAX_SCRATCH && !s; i++)
+        if (d->scratch[i].ptr && d->scratch[i].key == key) s = &d->scratch[i];
+    for (int i = 0; i < BC_MAX_SCRATCH && !s; i++)
+        if (!d->scratch[i].ptr) s = &d->scratch[i];
+    if (!s) {                                    /* table full: recycle entry 0 after draining the device */
+        cudaDeviceSynchronize();
+        s = &d->scratch[0];
+    }
+    int rc = BC_OK;
+    if (s->cap < bytes) {
+        if (s->ptr) { cudaDeviceSynchronize(); cudaFree(s->ptr); s->ptr = NULL; s->cap = 0; }
+        size_t cap = bytes < ((size_t)1 << 20) ? ((size_t)1 << 20) : bytes;
+        cudaError_t e = cudaMalloc(&s->ptr, cap);
+        if (e != cudaSuccess) { rc = bc_cuda_fail((int)e, "cudaMalloc(scratch)"); s->ptr = NULL; }
+        else s->cap = cap;
+    }
+    s->key = key;
+    *d_ptr = s->ptr;
+    pthread_mutex_unlock(&d->scratch_lock);
+    return rc;
+}
+
+/* ----------------------------------------------------- memory conveniences */
+
+void *bc_host_alloc(size_t bytes)
+{
+    void *p = NULL;
+    if (bc_set_device(tls_device)) return NULL;
+    cudaError_t e = cudaHostAlloc(&p, bytes ? bytes : 1, cudaHostAllocPortable);
+    if (e != cudaSuccess) { bc_cuda_fail((int)e, "cudaHostAlloc"); return NULL; }
+    return p;
+}
+
+void bc_host_free(void *p) { if (p) cudaFreeHost(p); }
+
+void *bc_dev_alloc(size_t bytes)
+{
+    void *p = NULL;
+    if (bc_set_device(tls_device)) return NULL;
+    cudaError_t e = cudaMalloc(&p, bytes ? bytes : 1);
+    if (e != cudaSuccess) { bc_cuda_fail((int)e, "cudaMalloc"); return NULL; }
+    return p;
+}
+
+void bc_dev_free(void *p) { if (p) cudaFree(p); }
+
+int bc_memcpy_h2d(void *d_dst, const void *h_src, size_t bytes)
+{
+    BC_CUDA(cudaMemcpy(d_dst, h_src, bytes, cudaMemcpyHostToDevice), "cudaMemcpy H2D");
+    return BC_OK;
+}
+
+int bc_memcpy_d2h(void *h_dst, const void *d_src, size_t bytes)
+{
+    BC_CUDA(cudaMemcpy(h_dst, d_src, bytes, cudaMemcpyDeviceToHost), "cudaMemcpy D2H");
+    return BC_OK;
+}
+
+int bc_device_sync(void)
+{
+    BC_CUDA(cudaDeviceSynchronize(), "cudaDeviceSynchronize");
+    return BC_OK;
+}
+
+/* ------------------------------------------------------- pipeline plumbing */
+
+static int dev_prepare(bc_dev **out)
+{
+    int rc = bc_set_device(tls_device);
+    if (rc) return rc;
+    bc_dev *d = cur_dev_state(NULL);
+    if (!d) { bc_set_error("no current CUDA device"); return BC_ERR_NO_DEVICE; }
+    *out = d;
+    return BC_OK;
+}
+
+/* called with d->lock held */
+static int dev_ensure_slots(bc_dev *d)
+{
+    if (d->ready) return BC_OK;
+    for (int i = 0; i < BC_SLOTS; i++) {
+        bc_slot *s = &d->slot[i];
+        BC_CUDA(cudaStreamCreateWithFlags(&s->stream, cudaStreamNonBlocking), "cudaStreamCreate");
+        BC_CUDA(cudaEventCreateWithFlags(&s->done, cudaEventDisableTiming), "cudaEventCreate");
+        BC_CUDA(cudaMalloc((void **)&s->d_buf, BC_CHUNK_BYTES), "cudaMalloc(pipeline buffer)");
+    }
+    d->ready = 1;
+    return BC_OK;
+}
+
+static int dev_ensure_aux(bc_dev *d, size_t bytes)
+{
+    if (d->aux_cap >= bytes) return BC_OK;
+    if (d->d_aux) { cudaDeviceSynchronize(); cudaFree(d->d_aux); d->d_aux = NULL; d->aux_cap = 0; }
+    size_t cap = bytes < 4096 ? 4096 : bytes;
+    BC_CUDA(cudaMalloc((void **)&d->d_aux, cap), "cudaMalloc(aux)");
+    d->aux_cap = cap;
+    return BC_OK;
+}
+
+static int slot_ensure_pinned(bc_slot *s)
+{
+    if (!s->pin_in)  BC_CUDA(cudaHostAlloc((void **)&s->pin_in,  BC_CHUNK_BYTES, cudaHostAllocDefault), "cudaHostAlloc(staging in)");
+    if (!s->pin_out) BC_CUDA(cudaHostAlloc((void **)&s->pin_out, BC_CHUNK_BYTES, cudaHostAllocDefault), "cudaHostAlloc(staging out)");
+    return BC_OK;
+}
+
+/* 0 = pageable host, 1 = pinned/registered host, 2 = device or managed */
+static int classify(const void *p)
+{
+    struct cudaPointerAttributes at;
+    if (!p) return 0;
+    if (cudaPointerGetAttributes(&at, p) != cudaSuccess) { cudaGetLastError(); return 0; }
+    if (at.type == cudaMemoryTypeHost) return 1;
+    if (at.type == cudaMemoryTypeDevice || at.type == cudaMemoryTypeManaged) return 2;
+    return 0;
+}
+
+/* wait for a slot's previous chunk and finish its staged copy-out */
+static int slot_retire(bc_slot *s)
+{
+    BC_CUDA(cudaEventSynchronize(s->done), "cudaEventSynchronize");
+    if (s->pend_dst) {
+        memcpy(s->pend_dst, s->pin_out, s->pend_len);
+        s->pend_dst = NULL;
+    }
+    return BC_OK;
+}
+
+/* One chunk's kernel: `d` holds n bytes that start at byte `off` of the caller's buffer. */
+typedef int (*chunk_fn)(void *arg, size_t chunk_idx, size_t off, size_t n, void *d, cudaStream_t st);
+
+/* Run `fn` over [in, in+nbytes) in chunks of `chunk` bytes (<= BC_CHUNK_BYTES),
+ * each chunk H2D -> fn (in place on the device) -> D2H on its own stream. */
+static int run_pipeline(bc_dev *d, const unsigned char *in, unsigned char *out, size_t nbytes,
+                        size_t chunk, chunk_fn fn, void *arg)
+{
+    const int in_pinned = in && classify(in) == 1, out_pinned = classify(out) == 1;
+    int rc = BC_OK;
+    size_t idx = 0;
+    for (size_t off = 0; off < nbytes && rc == BC_OK; off += chunk, idx++) {
+        const size_t n = nbytes - off < chunk ? nbytes - off : chunk;
+        bc_slot *s = &d->slot[idx % BC_SLOTS];
+        if (idx >= BC_SLOTS && (rc = slot_retire(s))) break;
+        cudaError_t e;
+        if ((in && !in_pinned) || !out_pinned) { if ((rc = slot_ensure_pinned(s))) break; }
+        if (in) {                                  /* in == NULL: the kernel only produces output */
+            const unsigned char *src = in + off;
+            if (!in_pinned) { memcpy(s->pin_in, src, n); src = s->pin_in; }
+            e = cudaMemcpyAsync(s->d_buf, src, n, cudaMemcpyHostToDevice, s->stream);
+            if (e != cudaSuccess) { rc = bc_cuda_fail((int)e, "cudaMemcpyAsync H2D"); break; }
+        }
+        if ((rc = fn(arg, idx, off, n, s->d_buf, s->stream))) break;
+        unsigned char *dst = out_pinned ? out + off : s->pin_out;
+        e = cudaMemcpyAsync(dst, s->d_buf, n, cudaMemcpyDeviceToHost, s->stream);
+        if (e != cudaSuccess) { rc = bc_cuda_fail((int)e, "cudaMemcpyAsync D2H"); break; }
+        if (!out_pinned) { s->pend_dst = out + off; s->pend_len = n; }
+        e = cudaEventRecord(s->done, s->stream);
+        if (e != cudaSuccess) { rc = bc_cuda_fail((int)e, "cudaEventRecord"); break; }
+    }
+    /* drain in issue order so staged copy-outs land even after an error */
+    const size_t issued = idx < BC_SLOTS ? idx : BC_SLOTS;
+    for (size_t k = 0; k < issued; k++) {
+        bc_slot *s = &d->slot[(idx - issued + k) % BC_SLOTS];
+        int r2 = slot_retire(s);
+        if (rc == BC_OK) rc = r2;
+    }
+    if (rc != BC_OK) { for (int k = 0; k < BC_SLOTS; k++) { cudaStreamSynchronize(d->slot[k].stream); d->slot[k].pend_dst = NULL; } }
+    return rc;
+}
+
+static int check_host_args(const uint32_t *rk, int nr, const void *in, const void *out, size_t nbytes)
+{
+    if (!rk || (nr != 10 && nr != 12 && nr != 14)) {
+        bc_set_error("bad key schedule (rk=%p, nr=%d; nr must be 10, 12 or 14)", (const void *)rk, nr);
+        return BC_ERR_BAD_ARG;
+    }
+    if (nbytes && (!in || !out)) { bc_set_error("NULL data pointer with nbytes=%zu", nbytes); return BC_ERR_BAD_ARG; }
+    return BC_OK;
+}
+
+/* ------------------------------------------------------------- AES-CTR */
+
+typedef struct {
+    const uint32_t *rk; int nr; const unsigned char *counter; int bits; uint64_t first_block;
+    size_t total; unsigned char *d_last;
+} ctr_op;
+
+static int ctr_chunk(void *arg, size_t idx, size_t off, size_t n, void *d, cudaStream_t st)
+{
+    ctr_op *o = (ctr_op *)arg;
+    (void)idx;
+    void *last = (o->d_last && off + n == o->total) ? o->d_last : NULL;
+    return bc_aes_ctr_dev(o->rk, o->nr, o->counter, o->bits, o->first_block + off / 16, d, d, n, last, st);
+}
+
+int bc_aes_ctr_host(const uint32_t *rk, int nr, const unsigned char counter[16], int counter_bits,
+                    uint64_t first_block, const void *in, void *out, size_t nbytes,
+                    unsigned char last_keystream[16])
+{
+    int rc = check_host_args(rk, nr, in, out, nbytes);
+    if (rc) return rc;
+    if (nbytes == 0) return BC_OK;
+    bc_dev *d;
+    if ((rc = dev_prepare(&d))) return rc;
+    if (classify(in) == 2 && classify(out) == 2) {           /* device-resident: no staging at all */
+        pthread_mutex_lock(&d->lock);
+        void *d_last = NULL;
+        if (last_keystream && (rc = dev_ensure_aux(d, 16)) == BC_OK) d_last = d->d_aux;
+        if (rc == BC_OK) rc = bc_aes_ctr_dev(rk, nr, counter, counter_bits, first_block, in, out, nbytes, d_last, NULL);
+        if (rc == BC_OK && d_last) rc = bc_memcpy_d2h(last_keystream, d_last, 16);
+        if (rc == BC_OK) rc = bc_device_sync();
+        pthread_mutex_unlock(&d->lock);
+        return rc;
+    }
+    pthread_mutex_lock(&d->lock);
+    if ((rc = dev_ensure_slots(d)) == BC_OK && (rc = dev_ensure_aux(d, 16)) == BC_OK) {
+        ctr_op o = { rk, nr, counter, counter_bits, first_block, nbytes, last_keystream ? d->d_aux : NULL };
+        rc = run_pipeline(d, (const unsigned char *)in, (unsigned char *)out, nbytes, BC_CHUNK_BYTES, ctr_chunk, &o);
+        if (rc == BC_OK && last_keystream) rc = bc_memcpy_d2h(last_keystream, d->d_aux, 16);
+    }
+    pthread_mutex_unlock(&d->lock);
+    return rc;
+}
+
+/* ------------------------------------------------------------- AES-ECB */
+
+typedef struct { const uint32_t *rk; int nr; int mode; } ecb_op;
+
+static int ecb_chunk(void *arg, size_t idx, size_t off, size_t n, void *d, cudaStream_t st)
+{
+    ecb_op *o = (ecb_op *)arg;
+    (void)idx; (void)off;
+    return bc_aes_ecb_dev(o->rk, o->nr, o->mode, d, d, n, st);
+}
+
+int bc_aes_ecb_host(const uint32_t *rk, int nr, int mode, const void *in, void *out, size_t nbytes)
+{
+    int rc = check_host_args(rk, nr, in, out, nbytes);
+    if (rc) return rc;
+    nbytes -= nbytes % 16;                                    /* whole blocks only */
+    if (nbytes == 0) return BC_OK;
+    bc_dev *d;
+    if ((rc = dev_prepare(&d))) return rc;
+    if (classify(in) == 2 && classify(out) == 2) {
+        rc = bc_aes_ecb_dev(rk, nr, mode, in, out, nbytes, NULL);
+        return rc ? rc : bc_device_sync();
+    }
+    pthread_mutex_lock(&d->lock);
+    if ((rc = dev_ensure_slots(d)) == BC_OK) {
+        ecb_op o = { rk, nr, mode };
+        rc = run_pipeline(d, (const unsigned char *)in, (unsigned char *)out, nbytes, BC_CHUNK_BYTES, ecb_chunk, &o);
+    }
+    pthread_mutex_unlock(&d->lock);
+    return rc;
+}
+
+/* ------------------------------------------------------ AES-CBC decrypt */
+
+typedef struct { const uint32_t *rk; int nr; const unsigned char *ivs; } cbcd_op;
+
+static int cbcd_chunk(void *arg, size_t idx, size_t off, size_t n, void *d, cudaStream_t st)
+{
+    cbcd_op *o = (cbcd_op *)arg;
+    (void)off;
+    return bc_aes_cbc_decrypt_dev(o->rk, o->nr, o->ivs + 16 * idx, d, d, n, st);
+}
+
+int bc_aes_cbc_decrypt_host(const uint32_t *rk, int nr, const unsigned char iv[16],
+                            const void *in, void *out, size_t nbytes)
+{
+    int rc = check_host_args(rk, nr, in, out, nbytes);
+    if (rc) return rc;
+    if (!iv) { bc_set_error("iv is NULL"); return BC_ERR_BAD_ARG; }
+    if (nbytes % 16) { bc_set_error("CBC length %zu is not a multiple of 16", nbytes); return BC_ERR_BAD_ARG; }
+    if (nbytes == 0) return BC_OK;
+    bc_dev *d;
+    if ((rc = dev_prepare(&d))) return rc;
+    if (classify(in) == 2 && classify(out) == 2) {
+        rc = bc_aes_cbc_decrypt_dev(rk, nr, iv, in, out, nbytes, NULL);
+        return rc ? rc : bc_device_sync();
+    }
+    /* Chunk k chains from the last ciphertext block of chunk k-1.  Collect those
+     * blocks first: with in == out the pipeline's D2H would overwrite them. */
+    const size_t n_chunks = (nbytes + BC_CHUNK_BYTES - 1) / BC_CHUNK_BYTES;
+    unsigned char *ivs = (unsigned char *)malloc(16 * n_chunks);
+    if (!ivs) { bc_set_error("out of host memory"); return BC_ERR_BAD_ARG; }
+    memcpy(ivs, iv, 16);
+    for (size_t k = 1; k < n_chunks; k++) memcpy(ivs + 16 * k, (const unsigned char *)in + k * BC_CHUNK_BYTES - 16, 16);
+    pthread_mutex_lock(&d->lock);
+    if ((rc = dev_ensure_slots(d)) == BC_OK) {
+        cbcd_op o = { rk, nr, ivs };
+        rc = run_pipeline(d, (const unsigned char *)in, (unsigned char *)out, nbytes, BC_CHUNK_BYTES, cbcd_chunk, &o);
+    }
+    pthread_mutex_unlock(&d->lock);
+    free(ivs);
+    return rc;
+}
+
+/* ------------------------------------------- AES-CBC encrypt, batched msgs */
+
+typedef struct {
+    const uint32_t *rk; int nr; size_t msg_len; size_t msgs_per_chunk;
+    const unsigned char *ivs; unsigned char *ivs_out; unsigned char *d_ivs;   /* [BC_SLOTS][msgs_per_chunk][16] */
+    size_t n_msgs;
+} cbce_op;
+
+static int cbce_chunk(void *arg, size_t idx, size_t off, size_t n, void *d, cudaStream_t st)
+{
+    cbce_op *o = (cbce_op *)arg;
+    const size_t m0 = off / o->msg_len, nm = n / o->msg_len;
+    unsigned char *d_iv = o->d_ivs + (idx % BC_SLOTS) * o->msgs_per_chunk * 16;
+    BC_CUDA(cudaMemcpyAsync(d_iv, o->ivs + 16 * m0, 16 * nm, cudaMemcpyHostToDevice, st), "cudaMemcpyAsync ivs");
+    int rc = bc_aes_cbc_encrypt_batch_dev(o->rk, o->nr, nm, o->msg_len, d_iv, o->ivs_out ? d_iv : NULL, d, d, st);
+    if (rc) return rc;
+    if (o->ivs_out)
+        BC_CUDA(cudaMemcpyAsync(o->ivs_out + 16 * m0, d_iv, 16 * nm, cudaMemcpyDeviceToHost, st), "cudaMemcpyAsync ivs_out");
+    return BC_OK;
+}
+
+int bc_aes_cbc_encrypt_batch_host(const uint32_t *rk, int nr, size_t n_msgs, size_t msg_len,
+                                  const void *ivs, void *ivs_out, const void *in, void *out)
+{
+    int rc = check_host_args(rk, nr, in, out, n_msgs * msg_len);
+    if (rc) return rc;
+    if (msg_len % 16) { bc_set_error("CBC message length %zu is not a multiple of 16", msg_len); return BC_ERR_BAD_ARG; }
+    if (n_msgs == 0 || msg_len == 0) return BC_OK;
+    if (!ivs) { bc_set_error("ivs is NULL"); return BC_ERR_BAD_ARG; }
+    bc_dev *d;
+    if ((rc = dev_prepare(&d))) return rc;
+    if (classify(in) == 2 && classify(out) == 2 && classify(ivs) == 2) {
+        rc = bc_aes_cbc_encrypt_batch_dev(rk, nr, n_msgs, msg_len, ivs, ivs_out, in, out, NULL);
+        return rc ? rc : bc_device_sync();
+    }
+    pthread_mutex_lock(&d->lock);
+    if ((rc = dev_ensure_slots(d)) == BC_OK) {
+        if (msg_len <= BC_CHUNK_BYTES) {
+            cbce_op o = { rk, nr, msg_len, BC_CHUNK_BYTES / msg_len, (const unsigned char *)ivs,
+                          (unsigned char *)ivs_out, NULL, n_msgs };
+            if ((rc = dev_ensure_aux(d, BC_SLOTS * o.msgs_per_chunk * 16)) == BC_OK) {
+                o.d_ivs = d->d_aux;
+                rc = run_pipeline(d, (const unsigned char *)in, (unsigned char *)out, n_msgs * msg_len,
+                                  o.msgs_per_chunk * msg_len, cbce_chunk, &o);
+            }
+        } else {
+            /* a message longer than one pipeline buffer: walk it in pieces, the chain value
+             * travels through ivs_out of one piece into ivs of the next */
+            unsigned char iv[16];
+            for (size_t m = 0; m < n_msgs && rc == BC_OK; m++) {
+                memcpy(iv, (const unsigned char *)ivs + 16 * m, 16);
+                for (size_t off = 0; off < msg_len && rc == BC_OK; off += BC_CHUNK_BYTES) {
+                    size_t n = msg_len - off < BC_CHUNK_BYTES ? msg_len - off : BC_CHUNK_BYTES;
+                    cbce_op o = { rk, nr, n, 1, iv, iv, NULL, 1 };
+                    if ((rc = dev_ensure_aux(d, BC_SLOTS * 16)) != BC_OK) break;
+                    o.d_ivs = d->d_aux;
+                    rc = run_pipeline(d, (const unsigned char *)in + m * msg_len + off,
+                                      (unsigned char *)out + m * msg_len + off, n, n, cbce_chunk, &o);
+                }
+                if (ivs_out) memcpy((unsigned char *)ivs_out + 16 * m, iv, 16);
+            }
+        }
+    }
+    pthread_mutex_unlock(&d->lock);
+    return rc;
+}
+
+/* ---------------------------------------------------------- RC4 batched */
+
+#define BC_ARC4_CTX_BYTES 264   /* sizeof(arc4_context): int x, int y, m[256] (arc4.h:35-41) */
+
+int bc_xor_dev(const void *d_a, const void *d_b, void *d_out, size_t nbytes, void *stream);
+
+typedef struct {
+    size_t length; unsigned keylen; size_t streams_per_chunk; int keystream_only;
+    const unsigned char *keys; const unsigned char *ctx_in; unsigned char *ctx_out;
+    unsigned char *d_keys;      /* [BC_SLOTS][streams_per_chunk][keylen] */
+    unsigned char *d_ctx;       /* [BC_SLOTS][streams_per_chunk][264] when contexts travel */
+} rc4_op;
+
+/* streams [s0, s0+ns) of the call, data (if any) already in `d` */
+static int rc4_issue(rc4_op *o, size_t slot, size_t s0, size_t ns, void *d, cudaStream_t st)
+{
+    unsigned char *d_keys = o->d_keys + slot * o->streams_per_chunk * o->keylen;
+    unsigned char *d_ctx = o->d_ctx ? o->d_ctx + slot * o->streams_per_chunk * BC_ARC4_CTX_BYTES : NULL;
+    if (o->ctx_in)
+        BC_CUDA(cudaMemcpyAsync(d_ctx, o->ctx_in + s0 * BC_ARC4_CTX_BYTES, ns * BC_ARC4_CTX_BYTES,
+                                cudaMemcpyHostToDevice, st), "cudaMemcpyAsync ctx_in");
+    else
+        BC_CUDA(cudaMemcpyAsync(d_keys, o->keys + s0 * o->keylen, ns * o->keylen, cudaMemcpyHostToDevice, st),
+                "cudaMemcpyAsync keys");
+    int rc = bc_arc4_batch_dev(ns, d_keys, o->keylen, o->length, o->keystream_only ? NULL : d, d,
+                               o->ctx_in ? d_ctx : NULL, o->ctx_out ? d_ctx : NULL, st);
+    if (rc) return rc;
+    if (o->ctx_out)
+        BC_CUDA(cudaMemcpyAsync(o->ctx_out + s0 * BC_ARC4_CTX_BYTES, d_ctx, ns * BC_ARC4_CTX_BYTES,
+                                cudaMemcpyDeviceToHost, st), "cudaMemcpyAsync ctx_out");
+    return BC_OK;
+}
+
+static int rc4_chunk(void *arg, size_t idx, size_t off, size_t n, void *d, cudaStream_t st)
+{
+    rc4_op *o = (rc4_op *)arg;
+    return rc4_issue(o, idx % BC_SLOTS, off / o->length, n / o->length, d, st);
+}
+
+/* in == NULL asks for the raw keystream (what arc4_prep produces, arc4.c:72-97). */
+int bc_arc4_batch_host(size_t n_streams, const void *keys, unsigned keylen, size_t length,
+                       const void *in, void *out, const void *ctx_in, void *ctx_out)
+{
+    if (n_streams == 0) return BC_OK;
+    if ((!keys && !ctx_in) || (!ctx_in && (keylen < 1 || keylen > 256))) {
+        bc_set_error("RC4 needs keys with 1 <= keylen <= 256 (got %u) or contexts to resume", keylen);
+        return BC_ERR_BAD_ARG;
+    }
+    if (length && !out) { bc_set_error("NULL output pointer"); return BC_ERR_BAD_ARG; }
+    bc_dev *d;
+    int rc = dev_prepare(&d);
+    if (rc) return rc;
+    if (!keylen) keylen = 1;
+    const int with_ctx = (ctx_in || ctx_out);
+    pthread_mutex_lock(&d->lock);
+    if ((rc = dev_ensure_slots(d)) == BC_OK) {
+        if (length <= BC_CHUNK_BYTES) {
+            /* whole streams per chunk */
+            size_t spc = length ? BC_CHUNK_BYTES / length : 4096;
+            if (spc > 65536) spc = 65536;
+            rc4_op o = { length, keylen, spc, in == NULL, (const unsigned char *)keys, (const unsigned char *)ctx_in,
+                         (unsigned char *)ctx_out, NULL, NULL };
+            size_t need_keys = (BC_SLOTS * spc * keylen + 255) & ~(size_t)255;
+            size_t need_ctx = with_ctx ? BC_SLOTS * spc * BC_ARC4_CTX_BYTES : 0;
+            if ((rc = dev_ensure_aux(d, need_keys + need_ctx)) == BC_OK) {
+                o.d_keys = d->d_aux;
+                o.d_ctx = with_ctx ? d->d_aux + need_keys : NULL;
+                if (length) {
+                    rc = run_pipeline(d, (const unsigned char *)in, (unsigned char *)out, n_streams * length,
+                                      spc * length, rc4_chunk, &o);
+                } else {
+                    /* key setup only (arc4_setup): nothing streams, the contexts come back */
+                    bc_slot *sl = &d->slot[0];
+                    for (size_t s0 = 0; s0 < n_streams && rc == BC_OK; s0 += spc) {
+                        size_t ns = n_streams - s0 < spc ? n_streams - s0 : spc;
+                        rc = rc4_issue(&o, 0, s0, ns, sl->d_buf, sl->stream);
+                        if (rc == BC_OK) {
+                            cudaError_t e = cudaStreamSynchronize(sl->stream);
+                            if (e != cudaSuccess) rc = bc_cuda_fail((int)e, "cudaStreamSynchronize");
+                        }
+                    }
+                }
+            }
+        } else {
+            /* a stream longer than one pipeline buffer: pieces chained through its context */
+            unsigned char ctx[BC_ARC4_CTX_BYTES];
+            for (size_t s = 0; s < n_streams && rc == BC_OK; s++) {
+                int have_ctx = 0;
+                if (ctx_in) { memcpy(ctx, (const unsigned char *)ctx_in + s * BC_ARC4_CTX_BYTES, BC_ARC4_CTX_BYTES); have_ctx = 1; }
+                for (size_t off = 0; off < length && rc == BC_OK; off += BC_CHUNK_BYTES) {
+                    size_t n = length - off < BC_CHUNK_BYTES ? length - off : BC_CHUNK_BYTES;
+                    rc4_op o = { n, keylen, 1, in == NULL, keys ? (const unsigned char *)keys + s * keylen : NULL,
+                                 have_ctx ? ctx : NULL, ctx, NULL, NULL };
+                    size_t need_keys = (BC_SLOTS * (size_t)keylen + 255) & ~(size_t)255;
+                    if ((rc = dev_ensure_aux(d, need_keys + BC_SLOTS * BC_ARC4_CTX_BYTES)) != BC_OK) break;
+                    o.d_keys = d->d_aux;
+                    o.d_ctx = d->d_aux + need_keys;
+                    rc = run_pipeline(d, in ? (const unsigned char *)in + s * length + off : NULL,
+                                      (unsigned char *)out + s * length + off, n, n, rc4_chunk, &o);
+                    have_ctx = 1;
+                }
+                if (ctx_out) memcpy((unsigned char *)ctx_out + s * BC_ARC4_CTX_BYTES, ctx, BC_ARC4_CTX_BYTES);
+            }
+        }
+    }
+    pthread_mutex_unlock(&d->lock);
+    return rc;
+}
+
+/* out = a ^ b on host buffers (arc4_crypt, arc4.c:101-112).  `a` rides the pipeline
+ * buffer, `b` a second device buffer per slot. */
+typedef struct { const unsigned char *b; unsigned char *d_b; int b_pinned; } xor_op;
+
+static int xor_chunk(void *arg, size_t idx, size_t off, size_t n, void *d, cudaStream_t st)
+{
+    xor_op *o = (xor_op *)arg;
+    unsigned char *d_b = o->d_b + (idx % BC_SLOTS) * BC_CHUNK_BYTES;
+    /* pageable `b` goes through a synchronous staged copy; fine for a memory-bound XOR */
+    if (o->b_pinned) BC_CUDA(cudaMemcpyAsync(d_b, o->b + off, n, cudaMemcpyHostToDevice, st), "cudaMemcpyAsync b");
+    else {
+        BC_CUDA(cudaStreamSynchronize(st), "cudaStreamSynchronize");
+        BC_CUDA(cudaMemcpy(d_b, o->b + off, n, cudaMemcpyHostToDevice), "cudaMemcpy b");
+    }
+    return bc_xor_dev(d, d_b, d, n, st);
+}
+
+int bc_xor_host(const void *a, const void *b, void *out, size_t nbytes)
+{
+    if (nbytes == 0) return BC_OK;
+    if (!a || !b || !out) { bc_set_error("NULL pointer"); return BC_ERR_BAD_ARG; }
+    bc_dev *d;
+    int rc = dev_prepare(&d);
+    if (rc) return rc;
+    pthread_mutex_lock(&d->lock);
+    if ((rc = dev_ensure_slots(d)) == BC_OK) {
+        void *d_b = NULL;
+        if ((rc = bc_scratch_get((void *)d, BC_SLOTS * BC_CHUNK_BYTES, &d_b)) == BC_OK) {
+            xor_op o = { (const unsigned char *)b, (unsigned char *)d_b, classify(b) == 1 };
+            rc = run_pipeline(d, (const unsigned char *)a, (unsigned char *)out, nbytes, BC_CHUNK_BYTES, xor_chunk, &o);
+        }
+    }
+    pthread_mutex_unlock(&d->lock);
+    return rc;
+}
+
+/* ------------------------------------------------------------ multi-GPU */
+
+typedef struct {
+    int device; const uint32_t *rk; int nr; const unsigned char *counter; int bits;
+    uint64_t first_block; const unsigned char *in; unsigned char *out; size_t nbytes; int rc;
+    char err[256];
+} shard_job;
+
+static void *shard_main(void *p)
+{
+    shard_job *j = (shard_job *)p;
+    j->rc = bc_set_device(j->device);
+    if (j->rc == BC_OK)
+        j->rc = bc_aes_ctr_host(j->rk, j->nr, j->counter, j->bits, j->first_block, j->in, j->out, j->nbytes, NULL);
+    if (j->rc != BC_OK) snprintf(j->err, sizeof j->err, "GPU %d: %s", j->device, bc_last_error());
+    return NULL;
+}
+
+/* Equal contiguous block ranges, remainder to the last GPU (the reference's
+ * slice rule, aes-modes/test.c:33-35, minus its bug of restarting the counter
+ * on every slice, :273-285): shard g starts its counter at first block index. */
+int bc_aes_ctr_host_multi(int n_gpus, const uint32_t *rk, int nr, const unsigned char counter[16],
+                          int counter_bits, const void *in, void *out, size_t nbytes)
+{
+    if (n_gpus < 1 || n_gpus > BC_MAX_DEVICES) { bc_set_error("n_gpus=%d out of range", n_gpus); return BC_ERR_BAD_ARG; }
+    int have = bc_device_count();
+    if (have < n_gpus) { bc_set_error("asked for %d GPUs, %d visible", n_gpus, have); return BC_ERR_NO_DEVICE; }
+    const size_t total_blocks = (nbytes + 15) / 16;
+    const size_t per = total_blocks / (size_t)n_gpus;
+    shard_job jobs[BC_MAX_DEVICES];
+    pthread_t th[BC_MAX_DEVICES];
+    int started = 0, rc = BC_OK;
+    for (int g = 0; g < n_gpus; g++) {
+        const size_t b0 = per * (size_t)g;
+        const size_t byte0 = b0 * 16;
+        const size_t byte1 = (g == n_gpus - 1) ? nbytes : (b0 + per) * 16;
+        shard_job *j = &jobs[g];
+        j->device = g; j->rk = rk; j->nr = nr; j->counter = counter; j->bits = counter_bits;
+        j->first_block = b0;
+        j->in = (const unsigned char *)in + byte0;
+        j->out = (unsigned char *)out + byte0;
+        j->nbytes = byte1 > byte0 ? byte1 - byte0 : 0;
+        j->rc = BC_OK; j->err[0] = 0;
+        if (pthread_create(&th[g], NULL, shard_main, j) != 0) { bc_set_error("pthread_create failed"); rc = BC_ERR_BAD_ARG; break; }
+        started++;
+    }
+    for (int g = 0; g < started; g++) {
+        pthread_join(th[g], NULL);
+        if (jobs[g].rc != BC_OK && rc == BC_OK) { rc = jobs[g].rc; bc_set_error("%s", jobs[g].err); }
+    }
+    return rc;
+}

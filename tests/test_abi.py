@@ -1,0 +1,116 @@
+"""CPU: the C-ABI library builds, loads, exports every symbol include/*.h
+declares, and its host-only logic (key schedules, argument checks) matches the
+oracle.  No cipher compute is attempted without a GPU."""
+import ctypes as C
+import os
+import re
+
+import numpy as np
+import pytest
+
+from conftest import ROOT
+
+ENC, DEC = 1, 0
+h = bytes.fromhex
+
+
+def header_functions():
+    names = set()
+    for hdr in ("aes.h", "aesni.h", "arc4.h", "rc4.h", "bulkcipher.h"):
+        text = open(os.path.join(ROOT, "include", hdr)).read()
+        text = re.sub(r"/\*.*?\*/", "", text, flags=re.S)
+        for m in re.finditer(r"^\s*(?:const\s+)?(?:unsigned\s+)?[A-Za-z_][\w ]*?[\s\*]+(\w+)\s*\(", text, flags=re.M):
+            n = m.group(1)
+            if n not in ("defined", "__attribute__", "aligned", "__declspec", "align"):
+                names.add(n)
+    return names
+
+
+def test_build_and_symbols(pkg):
+    import __graft_entry__ as g
+    g.build()
+    L = pkg.lib()
+    declared = header_functions()
+    assert len(declared) >= 40
+    assert set(pkg.DROPIN_SYMBOLS + pkg.BC_SYMBOLS) <= declared | {"bc_xor_dev", "bc_xor_host"}
+    for name in sorted(declared):
+        assert hasattr(L, name), f"libbulkcipher.so does not export {name} declared in include/"
+
+
+def test_struct_layouts(pkg):
+    """ABI of aes-modes/aes.h:41-47, arc4.h:35-41, rc4.h:43-47 (560 / 264 / 264 bytes)."""
+    assert C.sizeof(pkg.aes_context) == 560
+    assert C.sizeof(pkg.arc4_context) == 264
+    assert C.sizeof(pkg.rc4_state) == 264
+    assert pkg.aes_context.rk.offset == 8 and pkg.aes_context.buf.offset == 16
+    assert pkg.arc4_context.m.offset == 8 and pkg.rc4_state.index1.offset == 256
+
+
+def test_key_schedules_match_oracle(pkg, orc, golden):
+    rng = np.random.default_rng(3)
+    keys = [h(v["key"]) for v in golden["vectors"]["aes"]]
+    keys += [rng.integers(0, 256, n, dtype=np.uint8).tobytes() for n in (16, 24, 32) for _ in range(8)]
+    for key in keys:
+        rc, ctx = pkg.aes_setkey_enc(key)
+        assert rc == 0 and ctx.nr == len(key) // 4 + 6
+        assert C.addressof(ctx.rk.contents) == C.addressof(ctx.buf)        # rk points into buf (aes.c:466)
+        assert np.array_equal(pkg.schedule_words(ctx), orc.schedule(key, ENC))
+        assert all(ctx.buf[i] >> 32 == 0 for i in range(4 * (ctx.nr + 1)))  # upper halves zero
+        rc, ctx = pkg.aes_setkey_dec(key)
+        assert rc == 0 and np.array_equal(pkg.schedule_words(ctx), orc.schedule(key, DEC))
+        assert pkg.AES_Key_Expansion(key) == orc.packed_schedule(key, ENC)
+    for v in golden["vectors"]["aes"]:
+        rc, ctx = pkg.aes_setkey_enc(h(v["key"]))
+        assert pkg.schedule_words(ctx).astype("<u4").tobytes().hex() == v["enc_schedule"]
+        rc, ctx = pkg.aes_setkey_dec(h(v["key"]))
+        assert pkg.schedule_words(ctx).astype("<u4").tobytes().hex() == v["dec_schedule"]
+    v = golden["vectors"]["aesni_key256"]
+    assert pkg.AES_Key_Expansion(h(v["key"])).hex() == v["schedule"]     # aesni.c:38-77
+
+
+def test_error_codes_without_compute(pkg):
+    for bits in (0, 64, 129, 512):
+        rc, ctx = pkg.aes_setkey_enc(bytes(64), bits)
+        assert rc == pkg.ERR_INVALID_KEY_LENGTH and ctx.nr == 0           # ctx untouched (aes.c:455-461)
+        rc, ctx = pkg.aes_setkey_dec(bytes(64), bits)
+        assert rc == pkg.ERR_INVALID_KEY_LENGTH
+    rc, ctx = pkg.aes_setkey_enc(bytes(16))
+    rc, out, iv = pkg.aes_crypt_cbc(ctx, ENC, bytes(range(16)), bytes(17))
+    assert rc == pkg.ERR_INVALID_INPUT_LENGTH and iv == bytes(range(16))  # aes.c:767-768
+    rc, out, iv = pkg.aes_crypt_cbc(ctx, ENC, bytes(range(16)), b"")
+    assert rc == 0 and iv == bytes(range(16))                             # length 0 is a no-op
+    L = pkg.lib()
+    assert L.bc_aes_ecb_dev(None, 10, 1, None, None, 0, None) == pkg.BC_ERR_BAD_ARG
+    rk = np.zeros(60, np.uint32)
+    assert L.bc_aes_ecb_dev(rk.ctypes.data, 11, 1, None, None, 0, None) == pkg.BC_ERR_BAD_ARG
+    assert "nr" in pkg.last_error()
+    assert L.bc_aes_ctr_dev(rk.ctypes.data, 10, bytes(16), 96, 0, None, None, 0, None, None) == pkg.BC_ERR_BAD_ARG
+    assert L.bc_aes_cbc_decrypt_dev(rk.ctypes.data, 10, bytes(16), 16, 16, 24, None) == pkg.BC_ERR_BAD_ARG
+    assert L.bc_aes_ecb_dev(rk.ctypes.data, 10, 1, 4096, 4096 + 32, 64, None) == pkg.BC_ERR_OVERLAP
+
+
+def test_no_cpu_fallback(pkg):
+    """Without a CUDA device the compute entry points must fail, never emulate."""
+    import torch
+    if torch.cuda.is_available():
+        pytest.skip("GPU present")
+    L = pkg.lib()
+    assert L.bc_device_count() == 0
+    assert L.CheckAESSupport() == 0
+    rk = np.zeros(60, np.uint32)
+    buf = np.zeros(64, np.uint8)
+    rc = L.bc_aes_ecb_host(rk.ctypes.data, 10, 1, buf.ctypes.data, buf.ctypes.data, 64)
+    assert rc in (pkg.BC_ERR_NO_DEVICE, pkg.BC_ERR_CUDA) and not buf.any()
+
+
+def test_product_does_not_reference_oracle():
+    """The product path may not import, link or call anything under oracle/."""
+    pkgdir = os.path.join(ROOT, "our-tree_b200")
+    for dirpath, _, files in os.walk(pkgdir):
+        if os.path.basename(dirpath) == "build":
+            continue
+        for f in files:
+            if f.endswith((".c", ".cu", ".h", ".cuh", ".py", ".inc")) or f == "Makefile":
+                text = open(os.path.join(dirpath, f), errors="replace").read()
+                assert "liboracle" not in text and "orc_" not in text and "libref" not in text, f
+                assert not re.search(r"^\s*(import|from)\s+oracle", text, flags=re.M), f
