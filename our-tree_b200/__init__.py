@@ -63,7 +63,7 @@ class arc4_context(C.Structure):          # arc4.h:35-41
 
 
 class rc4_state(C.Structure):             # rc4.h:43-47
-    _fields_ = [("perm", C.c_char * 256), ("index1", C.c_int), ("index2", C.c_int)]
+    _fields_ = [("perm", C.c_ubyte * 256), ("index1", C.c_int), ("index2", C.c_int)]   # char perm[256] in C
 
 
 _lib = None
