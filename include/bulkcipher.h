@@ -87,6 +87,31 @@ int bc_aes_ecb_dev(const uint32_t *rk, int nr, int mode, const void *d_in, void 
 int bc_aes_cbc_decrypt_dev(const uint32_t *rk, int nr, const unsigned char iv[16],
                            const void *d_in, void *d_out, size_t nbytes, void *stream);
 
+/* No counterpart in the reference.  In-place CBC decrypt like
+ * bc_aes_cbc_decrypt_dev(d_in == d_out), for callers that must not trigger a
+ * device allocation: services that provision all their HBM up front and run
+ * against a fixed budget (a late cudaMalloc can fail or stall them), code that
+ * owns a memory pool and has to account for every byte on the device, and
+ * latency-sensitive paths where the device-wide synchronisation an allocation
+ * or free can imply would stall unrelated streams.  bc_aes_cbc_decrypt_dev
+ * grows a library-owned scratch buffer on demand; this entry point instead
+ * parks the per-4-KiB boundary blocks in a fixed 1 MiB array that is part of
+ * the library image (each GPU that loads the library holds it until exit) and
+ * calls no cudaMalloc / cudaFree or any other allocating routine.
+ *   - Limit: nbytes <= 256 MiB (65536 row-groups) per call, multiple of 16;
+ *     larger requests fail with BC_ERR_TOO_LARGE and touch nothing.  Longer
+ *     buffers: split on a multiple of 4096 bytes and pass the last ciphertext
+ *     block of one piece (read it before the call) as the iv of the next.
+ *   - The first call on each device looks up the array's device address
+ *     (cudaGetSymbolAddress, with that device current); make that first call
+ *     before starting any stream capture.
+ *   - All calls on a device share the one array, whatever the stream: two
+ *     calls whose kernels can overlap on the GPU race on it.  Order them (same
+ *     stream, or an event) — calls that follow one another need no clearing,
+ *     every entry a call reads it has just rewritten itself. */
+int bc_aes_cbc_decrypt_inplace_noalloc_dev(const uint32_t *rk, int nr, const unsigned char iv[16],
+                                           void *d_buf, size_t nbytes, void *stream);
+
 /* CBC encrypt of n_msgs independent messages of msg_len bytes each (multiple
  * of 16), message-major contiguous.  Each message is one aes_crypt_cbc(
  * AES_ENCRYPT) call of the reference (aes-modes/aes.c:801-812): serial inside a

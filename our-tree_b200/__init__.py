@@ -42,7 +42,7 @@ BC_SYMBOLS = [
     "bc_host_alloc", "bc_host_free", "bc_dev_alloc", "bc_dev_free", "bc_memcpy_h2d", "bc_memcpy_d2h",
     "bc_device_sync",
     "bc_aes_ctr_dev", "bc_aes_ecb_dev", "bc_aes_cbc_decrypt_dev", "bc_aes_cbc_encrypt_batch_dev",
-    "bc_arc4_batch_dev", "bc_xor_dev",
+    "bc_arc4_batch_dev", "bc_xor_dev", "bc_aes_cbc_decrypt_inplace_noalloc_dev",
     "bc_aes_ctr_host", "bc_aes_ecb_host", "bc_aes_cbc_decrypt_host", "bc_aes_cbc_encrypt_batch_host",
     "bc_arc4_batch_host", "bc_xor_host", "bc_aes_ctr_host_multi",
 ]
@@ -92,6 +92,7 @@ def lib() -> C.CDLL:
     L.bc_aes_ctr_dev.argtypes = [vp, i32, vp, i32, u64, vp, vp, sz, vp, vp]
     L.bc_aes_ecb_dev.argtypes = [vp, i32, i32, vp, vp, sz, vp]
     L.bc_aes_cbc_decrypt_dev.argtypes = [vp, i32, vp, vp, vp, sz, vp]
+    L.bc_aes_cbc_decrypt_inplace_noalloc_dev.argtypes = [vp, i32, vp, vp, sz, vp]
     L.bc_aes_cbc_encrypt_batch_dev.argtypes = [vp, i32, sz, sz, vp, vp, vp, vp, vp]
     L.bc_arc4_batch_dev.argtypes = [sz, vp, u32, sz, vp, vp, vp, vp, vp]
     L.bc_xor_dev.argtypes = [vp, vp, vp, sz, vp]

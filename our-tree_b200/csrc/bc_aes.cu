@@ -648,3 +648,84 @@ extern "C" int bc_aes_cbc_encrypt_batch_dev(const uint32_t *rk, int nr, size_t n
     default: return launch_cbc_enc<14>(ks, a, st);
     }
 }
+
+/* ------------------------------------------------ allocation-free variant */
+
+namespace {
+
+/* Boundary-block scratch for bc_aes_cbc_decrypt_inplace_noalloc_dev: one 16-byte
+ * ciphertext block per 4 KiB row-group.  It lives in the module image, so every
+ * GPU that loads libbulkcipher.so carries this 1 MiB until the process exits. */
+constexpr unsigned long long kNoAllocMaxGroups = 65536;                       /* 65536 x 4 KiB = 256 MiB per call */
+constexpr unsigned long long kNoAllocMaxBytes  = kNoAllocMaxGroups * 4096ull;
+static __device__ __align__(256) uint4 g_noalloc_boundary[kNoAllocMaxGroups];
+
+constexpr int kNoAllocMaxDevices = 64;
+uint4 *g_noalloc_dev_ptr[kNoAllocMaxDevices];   /* device address of the array, per device; 0 = not looked up yet */
+
+/* The array's name is only a host-side handle; the address a kernel can use has
+ * to be asked for, with the right device current. */
+int noalloc_scratch(uint4 **out)
+{
+    int dev = -1;
+    BC_CUDA(cudaGetDevice(&dev), "cudaGetDevice");
+    if (dev < 0 || dev >= kNoAllocMaxDevices) {
+        bc_set_error("device ordinal %d is outside the supported range 0..%d", dev, kNoAllocMaxDevices - 1);
+        return BC_ERR_BAD_ARG;
+    }
+    uint4 *p = __atomic_load_n(&g_noalloc_dev_ptr[dev], __ATOMIC_ACQUIRE);
+    if (!p) {
+        void *sym = nullptr;
+        BC_CUDA(cudaGetSymbolAddress(&sym, g_noalloc_boundary), "cudaGetSymbolAddress(g_noalloc_boundary)");
+        p = (uint4 *)sym;
+        __atomic_store_n(&g_noalloc_dev_ptr[dev], p, __ATOMIC_RELEASE);   /* racing threads store the same value */
+    }
+    *out = p;
+    return BC_OK;
+}
+
+}  // namespace
+
+/* See include/bulkcipher.h.  Same kernels as bc_aes_cbc_decrypt_dev with
+ * d_in == d_out; the only difference is where the boundary blocks are parked. */
+extern "C" int bc_aes_cbc_decrypt_inplace_noalloc_dev(const uint32_t *rk, int nr, const unsigned char iv[16],
+                                                      void *d_buf, size_t nbytes, void *stream)
+{
+    int rc = check_common(rk, nr, d_buf, d_buf, nbytes);
+    if (rc) return rc;
+    if (!iv) { bc_set_error("iv is NULL"); return BC_ERR_BAD_ARG; }
+    if (nbytes % 16) { bc_set_error("CBC length %zu is not a multiple of 16", nbytes); return BC_ERR_BAD_ARG; }
+    if (nbytes > kNoAllocMaxBytes) {
+        bc_set_error("bc_aes_cbc_decrypt_inplace_noalloc_dev handles at most %llu bytes per call (got %zu); "
+                     "split the buffer on a 4096-byte multiple and chain the iv, or use bc_aes_cbc_decrypt_dev",
+                     kNoAllocMaxBytes, nbytes);
+        return BC_ERR_TOO_LARGE;
+    }
+    if (nbytes == 0) return BC_OK;
+    uint4 *scratch = nullptr;
+    if ((rc = noalloc_scratch(&scratch))) return rc;
+
+    AesSched ks;
+    load_sched(ks, rk, nr);
+    BlkArgs a = {};
+    a.in = (const uint4 *)d_buf;
+    a.out = (uint4 *)d_buf;
+    a.nblocks = nbytes / 16;
+    a.n_groups = (a.nblocks + 255) / 256;
+    uint32_t w[4];
+    for (int i = 0; i < 4; i++)
+        w[i] = (uint32_t)iv[4 * i] | ((uint32_t)iv[4 * i + 1] << 8) | ((uint32_t)iv[4 * i + 2] << 16) |
+               ((uint32_t)iv[4 * i + 3] << 24);
+    a.iv = make_uint4(w[0], w[1], w[2], w[3]);
+    cudaStream_t st = (cudaStream_t)stream;
+    if (a.n_groups > 1) {
+        /* entries 1..n_groups-1 are rewritten here before the main kernel reads them, so
+         * nothing left over from an earlier call is ever consumed and nothing needs zeroing */
+        const int tpb = 256;
+        const unsigned blocks = (unsigned)((a.n_groups + tpb - 1) / tpb);
+        cbc_save_boundaries_kernel<<<blocks, tpb, 0, st>>>(a.in, scratch, a.n_groups);
+        BC_CUDA(cudaGetLastError(), "cbc_save_boundaries_kernel launch");
+        a.boundary = scratch;
+    }
+    return launch_blocks_nr<MODE_CBC_DEC>(nr, ks, a, st);
+}
