@@ -49,7 +49,7 @@ constexpr int kArrayBytes   = 65536;           /* two interleaved tables */
 constexpr int kEncSmemBytes = 2 * kArrayBytes; /* FT0|FT1, FT2|FT3 */
 constexpr int kDecSmemBytes = 3 * kArrayBytes; /* RT0|RT1, RT2|RT3, RSb×4|unused */
 constexpr int kRowsPerGroup = 8;               /* 8 rows × 32 lanes = 256 blocks = 4 KiB */
-constexpr int kGroupsPerChunk = 8;             /* CTR: groups handled per warp trip */
+constexpr int kMaxGroupsPerChunk = 8;          /* CTR: groups handled per warp trip (1, 2, 4 or 8) */
 
 struct AesSched { uint32_t rk[60]; };
 
@@ -192,6 +192,7 @@ struct CtrArgs {
     uint64_t nblocks;            /* whole 16-byte blocks */
     uint32_t tail;               /* bytes of a final partial block, 0..15 */
     uint64_t n_chunks;
+    uint32_t gpc;                /* groups per chunk: 8 for big buffers, fewer so small ones still fill the SMs */
     uint4 *last_ks;              /* optional: keystream of the last block touched */
 };
 
@@ -218,7 +219,7 @@ aes_ctr_kernel(const __grid_constant__ AesSched ks, const __grid_constant__ CtrA
         /* ---- per-group constants: lane i works on group chunk*8 + (i & 7) ---- */
         uint32_t C0, D0, D1, D2, D3;
         {
-            const uint64_t g = chunk * kGroupsPerChunk + (lane & (kGroupsPerChunk - 1));
+            const uint64_t g = chunk * a.gpc + (lane & (a.gpc - 1));
             const uint64_t lo = a.base_lo + (g << 8);
             const uint64_t hi = a.base_hi + ((a.carry128 && lo < a.base_lo) ? 1u : 0u);
             const uint32_t s0 = __byte_perm((uint32_t)(hi >> 32), 0, 0x0123) ^ ks.rk[0];
@@ -235,11 +236,11 @@ aes_ctr_kernel(const __grid_constant__ AesSched ks, const __grid_constant__ CtrA
             D3 = TB(OFF_T0, 0, X3) ^ TB(OFF_T2, 2, X1) ^ TB(OFF_T3, 3, X2) ^ ks.rk[11];
         }
 
-        const uint64_t v0 = chunk * (uint64_t)(kGroupsPerChunk * 256);   /* first virtual index */
-        const bool full = (v0 >= a.c_lo) && (v0 + kGroupsPerChunk * 256 <= a.c_lo + a.nblocks);
+        const uint64_t v0 = chunk * (uint64_t)(a.gpc * 256u);   /* first virtual index */
+        const bool full = (v0 >= a.c_lo) && (v0 + a.gpc * 256u <= a.c_lo + a.nblocks);
 
 #pragma unroll 1
-        for (int gi = 0; gi < kGroupsPerChunk; gi++) {
+        for (int gi = 0; gi < (int)a.gpc; gi++) {
             const uint32_t c0 = __shfl_sync(0xffffffffu, C0, gi);
             const uint32_t d0 = __shfl_sync(0xffffffffu, D0, gi);
             const uint32_t d1 = __shfl_sync(0xffffffffu, D1, gi);
@@ -549,7 +550,14 @@ extern "C" int bc_aes_ctr_dev(const uint32_t *rk, int nr, const unsigned char co
     a.nblocks = nbytes / 16;
     a.tail = (uint32_t)(nbytes % 16);
     const uint64_t nb_all = a.nblocks + (a.tail ? 1 : 0);
-    const uint64_t per_chunk = (uint64_t)kGroupsPerChunk * 256;
+    /* 8 groups per warp trip amortise the per-group constants best; small buffers use
+     * fewer so that there are still at least ~2 trips for every warp of a full grid */
+    const uint64_t n_groups = (a.c_lo + nb_all + 255) / 256;
+    const int sms = bc_cached_sm_count();
+    if (sms <= 0) return BC_ERR_CUDA;
+    a.gpc = kMaxGroupsPerChunk;
+    while (a.gpc > 1 && n_groups / a.gpc < (uint64_t)sms * kWarps * 2) a.gpc >>= 1;
+    const uint64_t per_chunk = (uint64_t)a.gpc * 256;
     a.n_chunks = (a.c_lo + nb_all + per_chunk - 1) / per_chunk;
     a.last_ks = (uint4 *)d_last_keystream;
     cudaStream_t st = (cudaStream_t)stream;

@@ -19,6 +19,7 @@
  * that serves 32 lanes per clock per SM -> 6.4 bytes/clk/SM; HBM needs only
  * 2 bytes of traffic per byte.  The issue bound binds.
  */
+#include <cuda.h>
 #include <cuda_runtime.h>
 #include <stdint.h>
 
@@ -185,6 +186,296 @@ rc4_batch_kernel(const __grid_constant__ Rc4Args a)
     }
 }
 
+/* ======================================================================
+ * TMA-staged variant (the fast path: length % 16 == 0, 16-byte aligned buffers)
+ *
+ * The plain kernel above lets every lane read/write its own stream with 16-byte
+ * global accesses: one LDG.128 touches 32 different lines and costs 32 data-pipe
+ * wavefronts (profiles/r1_summary.md: 40 % of the pipe).  Here the stream data
+ * moves as 2-D TMA boxes of 32 streams x 64 bytes ([n_streams][length] u8
+ * tensor, SWIZZLE_64B), one bulk-tensor load and one bulk-tensor store per warp
+ * per 64 keystream bytes, double buffered.  A lane then reaches its own row
+ * with four LDS.128 / STS.128 that the swizzle keeps conflict free, XORs the
+ * keystream in place and the box goes back with a TMA store.  Rows past
+ * n_streams and bytes past `length` are clipped by the TMA unit.
+ *
+ * Permutation layout (64 KB per 256-thread CTA): byte i of thread t lives at
+ * i*256 + b0(t), b0 = (t>>7)*128 + (t&31)*4 + ((t>>5)&3): the four warps of a
+ * half-CTA share words, lane L still only touches bank L, and the address is a
+ * single PRMT (index byte -> address byte 1, b0 -> byte 0).
+ * The m[x+1] load of the next step is issued one step early and patched when
+ * this step's swap lands on it, which halves the dependent chain per byte.
+ * ==================================================================== */
+
+constexpr int kSlab        = 64;                    /* keystream bytes per TMA box row */
+constexpr int kBoxBytes    = 32 * kSlab;            /* 2 KB per box */
+constexpr int kTmaWarps    = kRc4Threads / 32;
+constexpr int kTmaStageOff = kRc4Smem;              /* [warp][2][kBoxBytes] */
+constexpr int kTmaBarOff   = kTmaStageOff + kTmaWarps * 2 * kBoxBytes;
+constexpr int kTmaSmem     = kTmaBarOff + kTmaWarps * 2 * 8;
+
+struct Rc4TmaArgs {
+    uint64_t n_streams;
+    const unsigned char *keys;
+    uint32_t keylen;
+    uint64_t length;
+    uint32_t has_in;
+    const unsigned char *ctx_in;
+    unsigned char *ctx_out;
+};
+
+__device__ __forceinline__ uint32_t paddr(uint32_t i, uint32_t b0) { return __byte_perm(i, b0, 0x5504); }
+
+__device__ __forceinline__ void mbar_init(uint32_t bar, uint32_t count)
+{
+    asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" :: "r"(bar), "r"(count) : "memory");
+}
+
+__device__ __forceinline__ void mbar_expect_tx(uint32_t bar, uint32_t bytes)
+{
+    asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" :: "r"(bar), "r"(bytes) : "memory");
+}
+
+__device__ __forceinline__ void mbar_wait(uint32_t bar, uint32_t parity)
+{
+    asm volatile(
+        "{\n"
+        ".reg .pred p;\n"
+        "WAIT_LOOP:\n"
+        "mbarrier.try_wait.parity.shared::cta.b64 p, [%0], %1;\n"
+        "@p bra WAIT_DONE;\n"
+        "bra WAIT_LOOP;\n"
+        "WAIT_DONE:\n"
+        "}\n" :: "r"(bar), "r"(parity) : "memory");
+}
+
+__device__ __forceinline__ void tma_load_2d(uint32_t dst, const CUtensorMap *tm, uint32_t c0, uint32_t c1, uint32_t bar)
+{
+    asm volatile("cp.async.bulk.tensor.2d.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1, {%2, %3}], [%4];"
+                 :: "r"(dst), "l"(tm), "r"(c0), "r"(c1), "r"(bar) : "memory");
+}
+
+__device__ __forceinline__ void tma_store_2d(const CUtensorMap *tm, uint32_t c0, uint32_t c1, uint32_t src)
+{
+    asm volatile("cp.async.bulk.tensor.2d.global.shared::cta.bulk_group [%0, {%1, %2}], [%3];"
+                 :: "l"(tm), "r"(c0), "r"(c1), "r"(src) : "memory");
+    asm volatile("cp.async.bulk.commit_group;" ::: "memory");
+}
+
+__device__ __forceinline__ void tma_store_wait_read()
+{
+    asm volatile("cp.async.bulk.wait_group.read 0;" ::: "memory");
+}
+
+__device__ __forceinline__ void tma_store_wait_all()
+{
+    asm volatile("cp.async.bulk.wait_group 0;" ::: "memory");
+}
+
+__device__ __forceinline__ uint4 lds128(uint32_t a)
+{
+    uint4 v;
+    asm volatile("ld.shared.v4.u32 {%0,%1,%2,%3}, [%4];" : "=r"(v.x), "=r"(v.y), "=r"(v.z), "=r"(v.w) : "r"(a) : "memory");
+    return v;
+}
+
+__device__ __forceinline__ void sts128(uint32_t a, uint4 v)
+{
+    asm volatile("st.shared.v4.u32 [%0], {%1,%2,%3,%4};" :: "r"(a), "r"(v.x), "r"(v.y), "r"(v.z), "r"(v.w) : "memory");
+}
+
+/* PRGA step with the next step's m[x+1] in flight (arc4.c:82-91).
+ * ax = address of m[x] for THIS step (already advanced), a = m[x]. */
+struct Prga { uint32_t x, y, a, ax; };
+
+__device__ __forceinline__ uint32_t prga_next(Prga &p, uint32_t base, uint32_t b0)
+{
+    const uint32_t a = p.a, ax = p.ax;
+    p.y += a;
+    const uint32_t ay = base + paddr(p.y, b0);
+    p.x += 1;                                        /* index of the NEXT step */
+    const uint32_t axn = base + paddr(p.x, b0);
+    uint32_t an = lds8(axn);                         /* m[x+1], one step early */
+    const uint32_t b = lds8(ay);
+    sts8(ax, b);
+    sts8(ay, a);
+    if (ay == axn) an = a;                           /* this step's swap just wrote that slot */
+    const uint32_t k = lds8(base + paddr(a + b, b0));
+    p.a = an;
+    p.ax = axn;
+    return k;
+}
+
+template <bool KEY16>
+__global__ void __launch_bounds__(kRc4Threads, 2)
+rc4_batch_tma_kernel(const __grid_constant__ Rc4TmaArgs a, const __grid_constant__ CUtensorMap tm_in,
+                     const __grid_constant__ CUtensorMap tm_out)
+{
+    extern __shared__ __align__(1024) uint32_t smem[];
+    const uint32_t base = (uint32_t)__cvta_generic_to_shared(smem);
+    const uint32_t t = threadIdx.x, lane = t & 31u, warp = t >> 5;
+    const uint32_t b0 = ((t >> 7) << 7) | (lane << 2) | (warp & 3u);
+    const uint32_t stage = base + kTmaStageOff + warp * (2 * kBoxBytes);
+    const uint32_t bar = base + kTmaBarOff + warp * 16;
+    /* this lane's row inside a box, SWIZZLE_64B: 16-byte chunk c sits at chunk c ^ ((row>>1)&3) */
+    const uint32_t row_off = lane * kSlab, swz = (lane >> 1) & 3u;
+
+    if (lane == 0) { mbar_init(bar, 1); mbar_init(bar + 8, 1); }
+    asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+    __syncthreads();
+
+    uint32_t phases = 0u;                            /* bit b = parity to wait for on buffer b */
+    const uint64_t n_groups = (a.n_streams + 31) / 32;
+    const uint64_t n_warps = (uint64_t)gridDim.x * kTmaWarps;
+    const uint32_t n_slabs = (uint32_t)((a.length + kSlab - 1) / kSlab);
+
+    for (uint64_t sg = (uint64_t)blockIdx.x * kTmaWarps + warp; sg < n_groups; sg += n_warps) {
+        const uint64_t s = sg * 32 + lane;
+        const bool live = s < a.n_streams;
+        const uint32_t row0 = (uint32_t)(sg * 32);
+
+        /* first box on its way while the key schedule runs */
+        if (a.has_in && n_slabs && lane == 0) {
+            mbar_expect_tx(bar, kBoxBytes);
+            tma_load_2d(stage, &tm_in, 0, row0, bar);
+        }
+
+        Prga p = { 0u, 0u, 0u, 0u };
+        if (a.ctx_in) {
+            /* resume: x, y, m[] exactly as arc4_prep left them (arc4.c:93-94); idle lanes get an identity */
+            const unsigned char *c = a.ctx_in + (live ? s : 0) * kCtxBytes;
+            if (live) { p.x = *(const uint32_t *)c; p.y = *(const uint32_t *)(c + 4); }
+            for (int i = 0; i < 256; i++) sts8(base + paddr(i, b0), live ? (uint32_t)c[8 + i] : (uint32_t)i);
+        } else {
+            for (int i = 0; i < 256; i++) sts8(base + paddr(i, b0), i);
+            uint32_t j = 0;
+            if (KEY16) {
+                uint4 kv = make_uint4(0, 0, 0, 0);
+                if (live) kv = *(const uint4 *)(a.keys + s * 16);
+                const uint32_t kw[4] = { kv.x, kv.y, kv.z, kv.w };
+                for (int i0 = 0; i0 < 256; i0 += 16) {
+#pragma unroll
+                    for (int e = 0; e < 16; e++) {
+                        const uint32_t ai = base + paddr(i0 + e, b0);
+                        const uint32_t v = lds8(ai);
+                        j = j + v + ((kw[e >> 2] >> (8 * (e & 3))) & 0xffu);
+                        const uint32_t aj = base + paddr(j, b0);
+                        const uint32_t u = lds8(aj);
+                        sts8(ai, u);
+                        sts8(aj, v);
+                    }
+                }
+            } else {
+                const unsigned char *key = a.keys + (live ? s : 0) * a.keylen;
+                uint32_t k = 0;
+                for (int i = 0; i < 256; i++) {
+                    if (k >= a.keylen) k = 0;
+                    const uint32_t ai = base + paddr(i, b0);
+                    const uint32_t v = lds8(ai);
+                    j = j + v + key[k++];
+                    const uint32_t aj = base + paddr(j, b0);
+                    const uint32_t u = lds8(aj);
+                    sts8(ai, u);
+                    sts8(aj, v);
+                }
+            }
+        }
+        /* prime the one-step-ahead load: m[x+1] */
+        p.x += 1;
+        p.ax = base + paddr(p.x, b0);
+        p.a = lds8(p.ax);
+
+        for (uint32_t k = 0; k < n_slabs; k++) {
+            const uint32_t buf = k & 1u;
+            const uint32_t sbuf = stage + buf * kBoxBytes;
+            if (lane == 0 && k + 1 < n_slabs) {
+                tma_store_wait_read();               /* the other buffer's last store has left shared memory */
+                if (a.has_in) {
+                    mbar_expect_tx(bar + 8 * (buf ^ 1u), kBoxBytes);
+                    tma_load_2d(stage + (buf ^ 1u) * kBoxBytes, &tm_in, (k + 1) * kSlab, row0, bar + 8 * (buf ^ 1u));
+                }
+            }
+            __syncwarp();
+            if (a.has_in) { mbar_wait(bar + 8 * buf, (phases >> buf) & 1u); phases ^= 1u << buf; }
+            const uint32_t valid = (uint32_t)(a.length - (uint64_t)k * kSlab < kSlab ? a.length - (uint64_t)k * kSlab : kSlab);
+#pragma unroll
+            for (uint32_t c = 0; c < 4; c++) {
+                if (c * 16 < valid) {                /* length is a multiple of 16: whole chunks only */
+                    uint32_t w[4];
+#pragma unroll
+                    for (int q = 0; q < 4; q++) {
+                        uint32_t acc = prga_next(p, base, b0);
+                        acc = __byte_perm(acc, prga_next(p, base, b0), 0x3240);
+                        acc = __byte_perm(acc, prga_next(p, base, b0), 0x3410);
+                        acc = __byte_perm(acc, prga_next(p, base, b0), 0x4210);
+                        w[q] = acc;
+                    }
+                    const uint32_t sa = sbuf + row_off + ((c ^ swz) << 4);
+                    uint4 d = make_uint4(0, 0, 0, 0);
+                    if (a.has_in) d = lds128(sa);
+                    d.x ^= w[0]; d.y ^= w[1]; d.z ^= w[2]; d.w ^= w[3];
+                    sts128(sa, d);
+                }
+            }
+            asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
+            __syncwarp();
+            if (lane == 0) tma_store_2d(&tm_out, k * kSlab, row0, sbuf);
+        }
+        if (lane == 0) tma_store_wait_read();        /* both buffers reusable by the next stream group */
+        __syncwarp();
+
+        if (a.ctx_out && live) {
+            /* undo the one-step lookahead: the context holds the x of the last byte produced */
+            unsigned char *c = a.ctx_out + s * kCtxBytes;
+            *(uint32_t *)c = (p.x - 1) & 0xffu;
+            *(uint32_t *)(c + 4) = p.y & 0xffu;
+            for (int i = 0; i < 256; i++) c[8 + i] = (unsigned char)lds8(base + paddr(i, b0));
+        }
+    }
+    if (lane == 0) tma_store_wait_all();
+}
+
+typedef CUresult (*EncodeTiledFn)(CUtensorMap *, CUtensorMapDataType, cuuint32_t, void *, const cuuint64_t *,
+                                  const cuuint64_t *, const cuuint32_t *, const cuuint32_t *, CUtensorMapInterleave,
+                                  CUtensorMapSwizzle, CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
+
+int make_stream_tensor_map(CUtensorMap *tm, const void *ptr, uint64_t n_streams, uint64_t length)
+{
+    static EncodeTiledFn encode = nullptr;
+    if (!encode) {
+        void *fn = nullptr;
+        cudaDriverEntryPointQueryResult q;
+        BC_CUDA(cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &fn, cudaEnableDefault, &q), "cudaGetDriverEntryPoint");
+        if (!fn || q != cudaDriverEntryPointSuccess) { bc_set_error("cuTensorMapEncodeTiled is not available"); return BC_ERR_CUDA; }
+        encode = (EncodeTiledFn)fn;
+    }
+    const cuuint64_t dims[2] = { (cuuint64_t)length, (cuuint64_t)n_streams };
+    const cuuint64_t strides[1] = { (cuuint64_t)length };
+    const cuuint32_t box[2] = { (cuuint32_t)kSlab, 32u };
+    const cuuint32_t estr[2] = { 1u, 1u };
+    CUresult r = encode(tm, CU_TENSOR_MAP_DATA_TYPE_UINT8, 2, const_cast<void *>(ptr), dims, strides, box, estr,
+                        CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_64B, CU_TENSOR_MAP_L2_PROMOTION_NONE,
+                        CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+    if (r != CUDA_SUCCESS) { bc_set_error("cuTensorMapEncodeTiled failed (CUresult %d)", (int)r); return BC_ERR_CUDA; }
+    return BC_OK;
+}
+
+template <bool KEY16>
+int launch_rc4_tma(const Rc4TmaArgs &a, const CUtensorMap &tin, const CUtensorMap &tout, cudaStream_t st)
+{
+    BC_CUDA(cudaFuncSetAttribute(rc4_batch_tma_kernel<KEY16>, cudaFuncAttributeMaxDynamicSharedMemorySize, kTmaSmem),
+            "cudaFuncSetAttribute(rc4 tma smem)");
+    const int sms = bc_cached_sm_count();
+    if (sms <= 0) return BC_ERR_CUDA;
+    const uint64_t groups = (a.n_streams + 31) / 32;
+    const uint64_t ctas = (groups + kTmaWarps - 1) / kTmaWarps;
+    const uint64_t cap = (uint64_t)sms * 2;
+    const int grid = (int)(ctas < cap ? ctas : cap);
+    rc4_batch_tma_kernel<KEY16><<<grid, kRc4Threads, kTmaSmem, st>>>(a, tin, tout);
+    BC_CUDA(cudaGetLastError(), "rc4_batch_tma_kernel launch");
+    return BC_OK;
+}
+
 __global__ void xor_kernel(const uint4 *a, const uint4 *b, uint4 *o, uint64_t n16,
                            const unsigned char *ta, const unsigned char *tb, unsigned char *to, uint32_t tail)
 {
@@ -244,6 +535,22 @@ extern "C" int bc_arc4_batch_dev(size_t n_streams, const void *d_keys, unsigned 
     const bool vec = (length % 16 == 0) && !((((uintptr_t)d_in) | ((uintptr_t)d_out)) & 15u);
     const bool key16 = !d_ctx_in && keylen == 16 && !(((uintptr_t)d_keys) & 15u);
     cudaStream_t st = (cudaStream_t)stream;
+    if (vec && length >= 16 && length < ((size_t)1 << 32) && n_streams < ((size_t)1 << 31)) {
+        /* fast path: stream data staged through shared memory by TMA */
+        Rc4TmaArgs t;
+        t.n_streams = n_streams;
+        t.keys = (const unsigned char *)d_keys;
+        t.keylen = keylen;
+        t.length = length;
+        t.has_in = d_in != nullptr;
+        t.ctx_in = (const unsigned char *)d_ctx_in;
+        t.ctx_out = (unsigned char *)d_ctx_out;
+        CUtensorMap tin, tout;
+        int rc = make_stream_tensor_map(&tout, d_out, n_streams, length);
+        if (rc) return rc;
+        if ((rc = make_stream_tensor_map(&tin, d_in ? d_in : d_out, n_streams, length))) return rc;
+        return key16 ? launch_rc4_tma<true>(t, tin, tout, st) : launch_rc4_tma<false>(t, tin, tout, st);
+    }
     if (vec) return key16 ? launch_rc4<true, true>(a, st) : launch_rc4<true, false>(a, st);
     return key16 ? launch_rc4<false, true>(a, st) : launch_rc4<false, false>(a, st);
 }
