@@ -22,7 +22,7 @@ import os
 import numpy as np
 
 _HERE = os.path.dirname(os.path.abspath(__file__))
-LIB_PATH = os.path.join(_HERE, "libbulkcipher.so")
+LIB_PATH = os.environ.get("BULKCIPHER_LIB") or os.path.join(_HERE, "libbulkcipher.so")   # override: A/B builds only
 
 AES_ENCRYPT, AES_DECRYPT = 1, 0
 ERR_INVALID_KEY_LENGTH = -0x20

@@ -43,8 +43,24 @@ namespace {
 __constant__ uint8_t c_sbox[256]     = { BC_SBOX_INIT };
 __constant__ uint8_t c_inv_sbox[256] = { BC_INV_SBOX_INIT };
 
-constexpr int kThreads      = 512;
+#ifndef BC_BLK_THREADS
+#define BC_BLK_THREADS 1024
+#endif
+constexpr int kThreads      = BC_BLK_THREADS;    /* ECB / CBC kernels: CTA size */
 constexpr int kWarps        = kThreads / 32;
+#ifndef BC_CTR_ILP
+#define BC_CTR_ILP 2          /* rows in flight per thread in the CTR fast path */
+#endif
+#ifndef BC_CTR_PREFETCH
+#define BC_CTR_PREFETCH 1     /* fetch the next trip's plaintext before computing this trip's keystream */
+#endif
+#ifndef BC_CTR_F3
+#define BC_CTR_F3 1           /* keep round 1's eight per-lane lookups in registers for the whole kernel */
+#endif
+#ifndef BC_CTR_THREADS
+#define BC_CTR_THREADS 1024
+#endif
+constexpr int kCtrThreads   = BC_CTR_THREADS;      /* CTR kernel CTA size (512 or 1024) */
 constexpr int kArrayBytes   = 65536;           /* two interleaved tables */
 constexpr int kEncSmemBytes = 2 * kArrayBytes; /* FT0|FT1, FT2|FT3 */
 constexpr int kDecSmemBytes = 3 * kArrayBytes; /* RT0|RT1, RT2|RT3, RSb×4|unused */
@@ -196,10 +212,34 @@ struct CtrArgs {
     uint4 *last_ks;              /* optional: keystream of the last block touched */
 };
 
+/* Keystream block for one counter value: rounds 1-2 from the group constants
+ * (c0, d0..d3) and the lane's precomputed round-1 lookup f, then NR-3 full table
+ * rounds and the last round.  4 + 16*(NR-3) + 16 lookups (132 for AES-128). */
 template <int NR>
-__global__ void __launch_bounds__(kThreads, 1)
+__device__ __forceinline__ State ctr_keystream(uint32_t c0, uint32_t d0, uint32_t d1, uint32_t d2, uint32_t d3,
+                                               uint32_t f, const AesSched &ks, const Tb tb)
+{
+    const uint32_t x0 = c0 ^ f;
+    State s;
+    s.a = d0 ^ TB(OFF_T0, 0, x0);
+    s.b = d1 ^ TB(OFF_T3, 3, x0);
+    s.c = d2 ^ TB(OFF_T2, 2, x0);
+    s.d = d3 ^ TB(OFF_T1, 1, x0);
+#pragma unroll
+    for (int r = 3; r < NR; r++) s = enc_round(s, ks.rk + 4 * r, tb);
+    return enc_last(s, ks.rk + 4 * NR, tb);
+}
+
+__device__ __forceinline__ uint4 xor4(uint4 p, const State s)
+{
+    return make_uint4(p.x ^ s.a, p.y ^ s.b, p.z ^ s.c, p.w ^ s.d);
+}
+
+template <int NR, int THREADS>
+__global__ void __launch_bounds__(THREADS, 1)
 aes_ctr_kernel(const __grid_constant__ AesSched ks, const __grid_constant__ CtrArgs a)
 {
+    constexpr int WARPS = THREADS / 32;
     extern __shared__ __align__(1024) uint32_t smem[];
     fill_tables<false>(smem);
     __syncthreads();
@@ -208,15 +248,39 @@ aes_ctr_kernel(const __grid_constant__ AesSched ks, const __grid_constant__ CtrA
     Tb tb = { smem_base_u32(smem), lane * 4u };
     asm volatile("" : "+r"(tb.lane4));    /* pin table reads below the barrier */
 
+    /* Round 1's only varying lookup is FT3[j ^ k3] with j the last counter byte.  Row `it`
+     * of a group gives this lane j = it*32 + lane for EVERY group, so the eight values are
+     * fetched once per kernel and round 1 costs no lookup at all afterwards. */
     const uint32_t k3 = ks.rk[3] >> 24;
-    /* address of FT3[(j ^ k3)] for j = lane; row `it` flips bits of j above bit 4 */
+#if BC_CTR_F3
+    uint32_t f3[kRowsPerGroup];
+#pragma unroll
+    for (int it = 0; it < kRowsPerGroup; it++)
+        f3[it] = lds32<OFF_T3>(tb.base + (((((uint32_t)it * 32u + lane) ^ k3) & 0xffu) << 8 | tb.lane4));
+    /* the fast path walks rows in order, so the values rotate through f3[0..] instead of being indexed */
+#define F3(k) f3[k]
+#define F3_ROTATE()                                                                      \
+    do {                                                                                 \
+        uint32_t t_[BC_CTR_ILP];                                                         \
+        _Pragma("unroll") for (int k_ = 0; k_ < BC_CTR_ILP; k_++) t_[k_] = f3[k_];       \
+        _Pragma("unroll") for (int k_ = 0; k_ < kRowsPerGroup - BC_CTR_ILP; k_++) f3[k_] = f3[k_ + BC_CTR_ILP]; \
+        _Pragma("unroll") for (int k_ = 0; k_ < BC_CTR_ILP; k_++) f3[kRowsPerGroup - BC_CTR_ILP + k_] = t_[k_]; \
+    } while (0)
+#define F3_AT(it) f3[it]
+#else
     const uint32_t a3_lane = (((lane ^ k3) & 0xffu) << 8) | tb.lane4;
+    uint32_t f3_it = 0;                  /* row index << 13: flips the bits of j above bit 4 */
+#define F3(k) lds32<OFF_T3>(tb.base + (a3_lane ^ (f3_it + ((uint32_t)(k) << 13))))
+#define F3_ROTATE() do { f3_it = (f3_it + ((uint32_t)BC_CTR_ILP << 13)) & (7u << 13); } while (0)
+#define F3_AT(it) lds32<OFF_T3>(tb.base + (a3_lane ^ ((uint32_t)(it) << 13)))
+#endif
+
     const uint64_t nb_all = a.nblocks + (a.tail ? 1u : 0u);
-    const uint64_t warp_gid = (uint64_t)blockIdx.x * kWarps + (threadIdx.x >> 5);
-    const uint64_t n_warps = (uint64_t)gridDim.x * kWarps;
+    const uint64_t warp_gid = (uint64_t)blockIdx.x * WARPS + (threadIdx.x >> 5);
+    const uint64_t n_warps = (uint64_t)gridDim.x * WARPS;
 
     for (uint64_t chunk = warp_gid; chunk < a.n_chunks; chunk += n_warps) {
-        /* ---- per-group constants: lane i works on group chunk*8 + (i & 7) ---- */
+        /* ---- per-group constants: lane i works on group chunk*gpc + (i & (gpc-1)) ---- */
         uint32_t C0, D0, D1, D2, D3;
         {
             const uint64_t g = chunk * a.gpc + (lane & (a.gpc - 1));
@@ -239,6 +303,65 @@ aes_ctr_kernel(const __grid_constant__ AesSched ks, const __grid_constant__ CtrA
         const uint64_t v0 = chunk * (uint64_t)(a.gpc * 256u);   /* first virtual index */
         const bool full = (v0 >= a.c_lo) && (v0 + a.gpc * 256u <= a.c_lo + a.nblocks);
 
+        if (full) {
+            /* fast path: two rows in flight per thread, plaintext fetched two rows ahead */
+            const uint4 *pin = a.in + (v0 - a.c_lo) + lane;
+            uint4 *pout = a.out + (v0 - a.c_lo) + lane;
+#if BC_CTR_PREFETCH
+            uint4 q0 = ld_stream(pin), q1 = ld_stream(pin + (BC_CTR_ILP == 2 ? 32 : 0));
+#else
+            uint4 q0, q1;
+#endif
+            (void)q1;
+#pragma unroll 1
+            for (int gi = 0; gi < (int)a.gpc; gi++) {
+                const uint32_t c0 = __shfl_sync(0xffffffffu, C0, gi);
+                const uint32_t d0 = __shfl_sync(0xffffffffu, D0, gi);
+                const uint32_t d1 = __shfl_sync(0xffffffffu, D1, gi);
+                const uint32_t d2 = __shfl_sync(0xffffffffu, D2, gi);
+                const uint32_t d3 = __shfl_sync(0xffffffffu, D3, gi);
+                const bool last_group = (gi + 1 == (int)a.gpc);
+#pragma unroll 1
+                for (int it = 0; it < kRowsPerGroup; it += BC_CTR_ILP) {
+#if BC_CTR_ILP == 2
+#if BC_CTR_PREFETCH
+                    uint4 n0 = q0, n1 = q1;
+                    if (!(last_group && it + 2 >= kRowsPerGroup)) {       /* rows it+2, it+3 (may be the next group's) */
+                        n0 = ld_stream(pin + 64);
+                        n1 = ld_stream(pin + 96);
+                    }
+#else
+                    q0 = ld_stream(pin); q1 = ld_stream(pin + 32);
+#endif
+                    const State sA = ctr_keystream<NR>(c0, d0, d1, d2, d3, F3(0), ks, tb);
+                    const State sB = ctr_keystream<NR>(c0, d0, d1, d2, d3, F3(1), ks, tb);
+                    st_stream(pout, xor4(q0, sA));
+                    st_stream(pout + 32, xor4(q1, sB));
+#if BC_CTR_PREFETCH
+                    q0 = n0; q1 = n1;
+#endif
+                    pin += 64; pout += 64;
+#else
+#if BC_CTR_PREFETCH
+                    uint4 n0 = q0;
+                    if (!(last_group && it + 1 >= kRowsPerGroup)) n0 = ld_stream(pin + 32);
+#else
+                    q0 = ld_stream(pin);
+#endif
+                    const State sA = ctr_keystream<NR>(c0, d0, d1, d2, d3, F3(0), ks, tb);
+                    st_stream(pout, xor4(q0, sA));
+#if BC_CTR_PREFETCH
+                    q0 = n0;
+#endif
+                    pin += 32; pout += 32;
+#endif
+                    F3_ROTATE();
+                }
+            }
+            continue;
+        }
+
+        /* edge chunks: per-lane bounds, ragged tail, last-keystream output */
 #pragma unroll 1
         for (int gi = 0; gi < (int)a.gpc; gi++) {
             const uint32_t c0 = __shfl_sync(0xffffffffu, C0, gi);
@@ -247,42 +370,24 @@ aes_ctr_kernel(const __grid_constant__ AesSched ks, const __grid_constant__ CtrA
             const uint32_t d2 = __shfl_sync(0xffffffffu, D2, gi);
             const uint32_t d3 = __shfl_sync(0xffffffffu, D3, gi);
             const uint64_t vg = v0 + (uint64_t)gi * 256 + lane;          /* this lane's row-0 virtual index */
-
-#pragma unroll 2
-            for (int it = 0; it < kRowsPerGroup; it++) {
-                /* rounds 1-2 with the cached constants: 5 lookups instead of 32 */
-                const uint32_t x0 = c0 ^ lds32<OFF_T3>(tb.base + (a3_lane ^ ((uint32_t)it << 13)));
-                State s;
-                s.a = d0 ^ TB(OFF_T0, 0, x0);
-                s.b = d1 ^ TB(OFF_T3, 3, x0);
-                s.c = d2 ^ TB(OFF_T2, 2, x0);
-                s.d = d3 ^ TB(OFF_T1, 1, x0);
 #pragma unroll
-                for (int r = 3; r < NR; r++) s = enc_round(s, ks.rk + 4 * r, tb);
-                s = enc_last(s, ks.rk + 4 * NR, tb);
-
+            for (int it = 0; it < kRowsPerGroup; it++) {
                 const uint64_t v = vg + (uint64_t)it * 32;
                 const uint64_t b = v - a.c_lo;
-                if (full) {
-                    uint4 p = ld_stream(a.in + b);
-                    p.x ^= s.a; p.y ^= s.b; p.z ^= s.c; p.w ^= s.d;
-                    st_stream(a.out + b, p);
-                } else if (v >= a.c_lo && b < nb_all) {
-                    if (b < a.nblocks) {
-                        uint4 p = ld_stream(a.in + b);
-                        p.x ^= s.a; p.y ^= s.b; p.z ^= s.c; p.w ^= s.d;
-                        st_stream(a.out + b, p);
-                    } else {                                   /* ragged tail, byte-wise (aes.c:879-895) */
-                        const unsigned char *pi = (const unsigned char *)(a.in + b);
-                        unsigned char *po = (unsigned char *)(a.out + b);
-                        for (uint32_t i = 0; i < a.tail; i++) {
-                            const uint32_t q = i >> 2;
-                            const uint32_t w = q == 0 ? s.a : q == 1 ? s.b : q == 2 ? s.c : s.d;
-                            po[i] = pi[i] ^ (unsigned char)(w >> (8 * (i & 3)));
-                        }
+                if (!(v >= a.c_lo && b < nb_all)) continue;
+                const State s = ctr_keystream<NR>(c0, d0, d1, d2, d3, F3_AT(it), ks, tb);
+                if (b < a.nblocks) {
+                    st_stream(a.out + b, xor4(ld_stream(a.in + b), s));
+                } else {                                       /* ragged tail, byte-wise (aes.c:879-895) */
+                    const unsigned char *pi = (const unsigned char *)(a.in + b);
+                    unsigned char *po = (unsigned char *)(a.out + b);
+                    for (uint32_t i = 0; i < a.tail; i++) {
+                        const uint32_t q = i >> 2;
+                        const uint32_t w = q == 0 ? s.a : q == 1 ? s.b : q == 2 ? s.c : s.d;
+                        po[i] = pi[i] ^ (unsigned char)(w >> (8 * (i & 3)));
                     }
-                    if (a.last_ks && b == nb_all - 1) *a.last_ks = make_uint4(s.a, s.b, s.c, s.d);
                 }
+                if (a.last_ks && b == nb_all - 1) *a.last_ks = make_uint4(s.a, s.b, s.c, s.d);
             }
         }
     }
@@ -325,7 +430,7 @@ aes_blocks_kernel(const __grid_constant__ AesSched ks, const __grid_constant__ B
             if (g == 0) carry = a.iv;
             else carry = a.boundary ? a.boundary[g] : a.in[g * 256 - 1];
         }
-#pragma unroll 2
+#pragma unroll 1
         for (int it = 0; it < kRowsPerGroup; it++) {
             const uint64_t b = b0 + (uint64_t)it * 32;
             const bool live = full || b < a.nblocks;
@@ -463,16 +568,25 @@ int grid_for(uint64_t warp_items)
     return (int)(ctas < (uint64_t)sms ? ctas : (uint64_t)sms);
 }
 
+template <int NR, int THREADS>
+int launch_ctr_t(const AesSched &ks, const CtrArgs &a, cudaStream_t st)
+{
+    int rc = set_smem(aes_ctr_kernel<NR, THREADS>, kEncSmemBytes);
+    if (rc) return rc;
+    const int sms = bc_cached_sm_count();
+    if (sms <= 0) return BC_ERR_CUDA;
+    uint64_t ctas = (a.n_chunks + THREADS / 32 - 1) / (THREADS / 32);
+    if (ctas < 1) ctas = 1;
+    const int grid = (int)(ctas < (uint64_t)sms ? ctas : (uint64_t)sms);
+    aes_ctr_kernel<NR, THREADS><<<grid, THREADS, kEncSmemBytes, st>>>(ks, a);
+    BC_CUDA(cudaGetLastError(), "aes_ctr_kernel launch");
+    return BC_OK;
+}
+
 template <int NR>
 int launch_ctr(const AesSched &ks, const CtrArgs &a, cudaStream_t st)
 {
-    int rc = set_smem(aes_ctr_kernel<NR>, kEncSmemBytes);
-    if (rc) return rc;
-    int grid = grid_for(a.n_chunks);
-    if (grid < 0) return BC_ERR_CUDA;
-    aes_ctr_kernel<NR><<<grid, kThreads, kEncSmemBytes, st>>>(ks, a);
-    BC_CUDA(cudaGetLastError(), "aes_ctr_kernel launch");
-    return BC_OK;
+    return launch_ctr_t<NR, kCtrThreads>(ks, a, st);
 }
 
 template <int NR, int MODE>
@@ -556,7 +670,7 @@ extern "C" int bc_aes_ctr_dev(const uint32_t *rk, int nr, const unsigned char co
     const int sms = bc_cached_sm_count();
     if (sms <= 0) return BC_ERR_CUDA;
     a.gpc = kMaxGroupsPerChunk;
-    while (a.gpc > 1 && n_groups / a.gpc < (uint64_t)sms * kWarps * 2) a.gpc >>= 1;
+    while (a.gpc > 1 && n_groups / a.gpc < (uint64_t)sms * (kCtrThreads / 32) * 2) a.gpc >>= 1;
     const uint64_t per_chunk = (uint64_t)a.gpc * 256;
     a.n_chunks = (a.c_lo + nb_all + per_chunk - 1) / per_chunk;
     a.last_ks = (uint4 *)d_last_keystream;
