@@ -36,6 +36,7 @@
 
 #include "bulkcipher.h"
 #include "bc_internal.h"
+#include "bc_tma.cuh"
 #include "bc_sbox.inc"
 
 namespace {
@@ -517,6 +518,78 @@ aes_cbc_enc_batch_kernel(const __grid_constant__ AesSched ks, const __grid_const
     }
 }
 
+/* TMA-staged form of the batch kernel (bc_tma.cuh): a warp owns 32 messages and moves
+ * boxes of 32 messages x 64 bytes (4 blocks of each chain) with one bulk-tensor load
+ * and one store, double buffered, so the global side is coalesced although every
+ * lane walks its own message.  The chain value never leaves registers. */
+constexpr int kCbcTmaMaxWarps = 24;          /* 128 KB tables + 24 x 4 KB staging fits 227 KB */
+
+template <int NR>
+__global__ void __launch_bounds__(kCbcTmaMaxWarps * 32, 1)
+aes_cbc_enc_batch_tma_kernel(const __grid_constant__ AesSched ks, const __grid_constant__ CbcEncArgs a,
+                             const __grid_constant__ CUtensorMap tm_in, const __grid_constant__ CUtensorMap tm_out)
+{
+    extern __shared__ __align__(1024) uint32_t smem[];
+    fill_tables<false>(smem);
+    const uint32_t lane = threadIdx.x & 31u, warp = threadIdx.x >> 5, warps = blockDim.x >> 5;
+    Tb tb = { smem_base_u32(smem), lane * 4u };
+    const uint32_t stage = tb.base + kEncSmemBytes + warp * (2 * kBoxBytes);
+    const uint32_t bar = tb.base + kEncSmemBytes + warps * (2 * kBoxBytes) + warp * 16;
+    if (lane == 0) { mbar_init(bar, 1); mbar_init(bar + 8, 1); }
+    asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+    __syncthreads();
+    asm volatile("" : "+r"(tb.lane4));
+
+    uint32_t phases = 0u;
+    const uint64_t msg_len = a.blocks_per_msg * 16;
+    const uint32_t n_slabs = (uint32_t)((msg_len + kSlab - 1) / kSlab);
+    const uint64_t n_groups = (a.n_msgs + 31) / 32;
+    const uint64_t n_warps = (uint64_t)gridDim.x * warps;
+
+    for (uint64_t mg = (uint64_t)blockIdx.x * warps + warp; mg < n_groups; mg += n_warps) {
+        const uint64_t m = mg * 32 + lane;
+        const bool live = m < a.n_msgs;
+        const uint32_t row0 = (uint32_t)(mg * 32);
+        if (lane == 0) {
+            mbar_expect_tx(bar, kBoxBytes);
+            tma_load_2d(stage, &tm_in, 0, row0, bar);
+        }
+        uint4 c = make_uint4(0, 0, 0, 0);
+        if (live) c = a.ivs[m];
+        for (uint32_t k = 0; k < n_slabs; k++) {
+            const uint32_t buf = k & 1u;
+            const uint32_t sbuf = stage + buf * kBoxBytes;
+            if (lane == 0 && k + 1 < n_slabs) {
+                tma_store_wait_read();
+                mbar_expect_tx(bar + 8 * (buf ^ 1u), kBoxBytes);
+                tma_load_2d(stage + (buf ^ 1u) * kBoxBytes, &tm_in, (k + 1) * kSlab, row0, bar + 8 * (buf ^ 1u));
+            }
+            __syncwarp();
+            mbar_wait(bar + 8 * buf, (phases >> buf) & 1u);
+            phases ^= 1u << buf;
+            const uint32_t valid = (uint32_t)(msg_len - (uint64_t)k * kSlab < kSlab ? msg_len - (uint64_t)k * kSlab : kSlab);
+#pragma unroll 1
+            for (uint32_t q = 0; q < 4; q++) {
+                if (q * 16 < valid) {
+                    const uint32_t sa = sbuf + box_chunk_off(lane, q);
+                    const uint4 pt = lds128(sa);
+                    State s = { pt.x ^ c.x, pt.y ^ c.y, pt.z ^ c.z, pt.w ^ c.w };    /* aes.c:803-804 */
+                    s = cipher_block<NR, false>(s, ks, tb);
+                    c = make_uint4(s.a, s.b, s.c, s.d);
+                    sts128(sa, c);
+                }
+            }
+            asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
+            __syncwarp();
+            if (lane == 0) tma_store_2d(&tm_out, k * kSlab, row0, sbuf);
+        }
+        if (lane == 0) tma_store_wait_read();
+        __syncwarp();
+        if (a.ivs_out && live) a.ivs_out[m] = c;     /* iv <- last ciphertext block (aes.c:807) */
+    }
+    if (lane == 0) tma_store_wait_all();
+}
+
 /* ------------------------------------------------------------ host helpers */
 
 int check_common(const uint32_t *rk, int nr, const void *in, const void *out, size_t nbytes)
@@ -615,11 +688,30 @@ int launch_blocks_nr(int nr, const AesSched &ks, const BlkArgs &a, cudaStream_t 
 template <int NR>
 int launch_cbc_enc(const AesSched &ks, const CbcEncArgs &a, cudaStream_t st)
 {
+    const int sms = bc_cached_sm_count();
+    if (sms <= 0) return BC_ERR_CUDA;
+    const uint64_t msg_len = a.blocks_per_msg * 16;
+    if (msg_len < ((uint64_t)1 << 32) && a.n_msgs < ((uint64_t)1 << 31)) {
+        /* TMA-staged: warps per CTA chosen so the message groups spread evenly over the SMs */
+        const uint64_t groups = (a.n_msgs + 31) / 32;
+        uint64_t warps = (groups + sms - 1) / sms;
+        if (warps > kCbcTmaMaxWarps) warps = kCbcTmaMaxWarps;
+        if (warps < 1) warps = 1;
+        const uint64_t ctas = (groups + warps - 1) / warps;
+        const int grid = (int)(ctas < (uint64_t)sms ? ctas : (uint64_t)sms);
+        const int smem = kEncSmemBytes + (int)warps * (2 * kBoxBytes + 16);
+        CUtensorMap tin, tout;
+        int rc = make_row_tensor_map(&tin, a.in, a.n_msgs, msg_len);
+        if (rc) return rc;
+        if ((rc = make_row_tensor_map(&tout, a.out, a.n_msgs, msg_len))) return rc;
+        if ((rc = set_smem(aes_cbc_enc_batch_tma_kernel<NR>, kEncSmemBytes + kCbcTmaMaxWarps * (2 * kBoxBytes + 16)))) return rc;
+        aes_cbc_enc_batch_tma_kernel<NR><<<grid, (int)warps * 32, smem, st>>>(ks, a, tin, tout);
+        BC_CUDA(cudaGetLastError(), "aes_cbc_enc_batch_tma_kernel launch");
+        return BC_OK;
+    }
     int rc = set_smem(aes_cbc_enc_batch_kernel<NR>, kEncSmemBytes);
     if (rc) return rc;
-    int sms = bc_cached_sm_count();
-    if (sms <= 0) return BC_ERR_CUDA;
-    /* spread the messages evenly: ceil(n/SMs) threads per CTA, whole warps, <= 512 */
+    /* spread the messages evenly: ceil(n/SMs) threads per CTA, whole warps, <= kThreads */
     uint64_t per = (a.n_msgs + sms - 1) / sms;
     per = ((per + 31) / 32) * 32;
     if (per > kThreads) per = kThreads;

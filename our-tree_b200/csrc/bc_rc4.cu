@@ -25,6 +25,7 @@
 
 #include "bulkcipher.h"
 #include "bc_internal.h"
+#include "bc_tma.cuh"
 
 namespace {
 
@@ -207,8 +208,6 @@ rc4_batch_kernel(const __grid_constant__ Rc4Args a)
  * this step's swap lands on it, which halves the dependent chain per byte.
  * ==================================================================== */
 
-constexpr int kSlab        = 64;                    /* keystream bytes per TMA box row */
-constexpr int kBoxBytes    = 32 * kSlab;            /* 2 KB per box */
 constexpr int kTmaWarps    = kRc4Threads / 32;
 constexpr int kTmaStageOff = kRc4Smem;              /* [warp][2][kBoxBytes] */
 constexpr int kTmaBarOff   = kTmaStageOff + kTmaWarps * 2 * kBoxBytes;
@@ -225,64 +224,6 @@ struct Rc4TmaArgs {
 };
 
 __device__ __forceinline__ uint32_t paddr(uint32_t i, uint32_t b0) { return __byte_perm(i, b0, 0x5504); }
-
-__device__ __forceinline__ void mbar_init(uint32_t bar, uint32_t count)
-{
-    asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" :: "r"(bar), "r"(count) : "memory");
-}
-
-__device__ __forceinline__ void mbar_expect_tx(uint32_t bar, uint32_t bytes)
-{
-    asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" :: "r"(bar), "r"(bytes) : "memory");
-}
-
-__device__ __forceinline__ void mbar_wait(uint32_t bar, uint32_t parity)
-{
-    asm volatile(
-        "{\n"
-        ".reg .pred p;\n"
-        "WAIT_LOOP:\n"
-        "mbarrier.try_wait.parity.shared::cta.b64 p, [%0], %1;\n"
-        "@p bra WAIT_DONE;\n"
-        "bra WAIT_LOOP;\n"
-        "WAIT_DONE:\n"
-        "}\n" :: "r"(bar), "r"(parity) : "memory");
-}
-
-__device__ __forceinline__ void tma_load_2d(uint32_t dst, const CUtensorMap *tm, uint32_t c0, uint32_t c1, uint32_t bar)
-{
-    asm volatile("cp.async.bulk.tensor.2d.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1, {%2, %3}], [%4];"
-                 :: "r"(dst), "l"(tm), "r"(c0), "r"(c1), "r"(bar) : "memory");
-}
-
-__device__ __forceinline__ void tma_store_2d(const CUtensorMap *tm, uint32_t c0, uint32_t c1, uint32_t src)
-{
-    asm volatile("cp.async.bulk.tensor.2d.global.shared::cta.bulk_group [%0, {%1, %2}], [%3];"
-                 :: "l"(tm), "r"(c0), "r"(c1), "r"(src) : "memory");
-    asm volatile("cp.async.bulk.commit_group;" ::: "memory");
-}
-
-__device__ __forceinline__ void tma_store_wait_read()
-{
-    asm volatile("cp.async.bulk.wait_group.read 0;" ::: "memory");
-}
-
-__device__ __forceinline__ void tma_store_wait_all()
-{
-    asm volatile("cp.async.bulk.wait_group 0;" ::: "memory");
-}
-
-__device__ __forceinline__ uint4 lds128(uint32_t a)
-{
-    uint4 v;
-    asm volatile("ld.shared.v4.u32 {%0,%1,%2,%3}, [%4];" : "=r"(v.x), "=r"(v.y), "=r"(v.z), "=r"(v.w) : "r"(a) : "memory");
-    return v;
-}
-
-__device__ __forceinline__ void sts128(uint32_t a, uint4 v)
-{
-    asm volatile("st.shared.v4.u32 [%0], {%1,%2,%3,%4};" :: "r"(a), "r"(v.x), "r"(v.y), "r"(v.z), "r"(v.w) : "memory");
-}
 
 /* PRGA step with the next step's m[x+1] in flight (arc4.c:82-91).
  * ax = address of m[x] for THIS step (already advanced), a = m[x]. */
@@ -435,31 +376,6 @@ rc4_batch_tma_kernel(const __grid_constant__ Rc4TmaArgs a, const __grid_constant
     if (lane == 0) tma_store_wait_all();
 }
 
-typedef CUresult (*EncodeTiledFn)(CUtensorMap *, CUtensorMapDataType, cuuint32_t, void *, const cuuint64_t *,
-                                  const cuuint64_t *, const cuuint32_t *, const cuuint32_t *, CUtensorMapInterleave,
-                                  CUtensorMapSwizzle, CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
-
-int make_stream_tensor_map(CUtensorMap *tm, const void *ptr, uint64_t n_streams, uint64_t length)
-{
-    static EncodeTiledFn encode = nullptr;
-    if (!encode) {
-        void *fn = nullptr;
-        cudaDriverEntryPointQueryResult q;
-        BC_CUDA(cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &fn, cudaEnableDefault, &q), "cudaGetDriverEntryPoint");
-        if (!fn || q != cudaDriverEntryPointSuccess) { bc_set_error("cuTensorMapEncodeTiled is not available"); return BC_ERR_CUDA; }
-        encode = (EncodeTiledFn)fn;
-    }
-    const cuuint64_t dims[2] = { (cuuint64_t)length, (cuuint64_t)n_streams };
-    const cuuint64_t strides[1] = { (cuuint64_t)length };
-    const cuuint32_t box[2] = { (cuuint32_t)kSlab, 32u };
-    const cuuint32_t estr[2] = { 1u, 1u };
-    CUresult r = encode(tm, CU_TENSOR_MAP_DATA_TYPE_UINT8, 2, const_cast<void *>(ptr), dims, strides, box, estr,
-                        CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_64B, CU_TENSOR_MAP_L2_PROMOTION_NONE,
-                        CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
-    if (r != CUDA_SUCCESS) { bc_set_error("cuTensorMapEncodeTiled failed (CUresult %d)", (int)r); return BC_ERR_CUDA; }
-    return BC_OK;
-}
-
 template <bool KEY16>
 int launch_rc4_tma(const Rc4TmaArgs &a, const CUtensorMap &tin, const CUtensorMap &tout, cudaStream_t st)
 {
@@ -546,9 +462,9 @@ extern "C" int bc_arc4_batch_dev(size_t n_streams, const void *d_keys, unsigned 
         t.ctx_in = (const unsigned char *)d_ctx_in;
         t.ctx_out = (unsigned char *)d_ctx_out;
         CUtensorMap tin, tout;
-        int rc = make_stream_tensor_map(&tout, d_out, n_streams, length);
+        int rc = make_row_tensor_map(&tout, d_out, n_streams, length);
         if (rc) return rc;
-        if ((rc = make_stream_tensor_map(&tin, d_in ? d_in : d_out, n_streams, length))) return rc;
+        if ((rc = make_row_tensor_map(&tin, d_in ? d_in : d_out, n_streams, length))) return rc;
         return key16 ? launch_rc4_tma<true>(t, tin, tout, st) : launch_rc4_tma<false>(t, tin, tout, st);
     }
     if (vec) return key16 ? launch_rc4<true, true>(a, st) : launch_rc4<true, false>(a, st);

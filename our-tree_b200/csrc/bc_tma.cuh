@@ -1,0 +1,116 @@
+/*
+ * bc_tma.cuh — TMA plumbing shared by the batched kernels (RC4 streams, CBC-encrypt
+ * messages): every lane of a warp walks its own row of a [rows][row_bytes] byte
+ * matrix, which as plain per-lane 16-byte accesses costs one data-pipe wavefront
+ * per lane.  Instead a warp moves boxes of 32 rows x 64 bytes with one bulk-tensor
+ * copy each way (cp.async.bulk.tensor.2d, SWIZZLE_64B so a lane's LDS.128/STS.128
+ * on its row are conflict free); rows/bytes outside the matrix are clipped by the
+ * TMA unit.  sm_100a only.
+ */
+#ifndef BC_TMA_CUH
+#define BC_TMA_CUH
+
+#include <cuda.h>
+#include <cuda_runtime.h>
+#include <stdint.h>
+
+#include "bulkcipher.h"
+#include "bc_internal.h"
+
+namespace {
+
+constexpr int kSlab     = 64;            /* bytes of one row per box */
+constexpr int kBoxBytes = 32 * kSlab;    /* 2 KB per box */
+
+/* byte offset of 16-byte chunk c (0..3) of row `lane` inside a SWIZZLE_64B box */
+__device__ __forceinline__ uint32_t box_chunk_off(uint32_t lane, uint32_t c)
+{
+    return lane * kSlab + ((c ^ ((lane >> 1) & 3u)) << 4);
+}
+
+__device__ __forceinline__ void mbar_init(uint32_t bar, uint32_t count)
+{
+    asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" :: "r"(bar), "r"(count) : "memory");
+}
+
+__device__ __forceinline__ void mbar_expect_tx(uint32_t bar, uint32_t bytes)
+{
+    asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" :: "r"(bar), "r"(bytes) : "memory");
+}
+
+__device__ __forceinline__ void mbar_wait(uint32_t bar, uint32_t parity)
+{
+    asm volatile(
+        "{\n"
+        ".reg .pred p;\n"
+        "WAIT_LOOP:\n"
+        "mbarrier.try_wait.parity.shared::cta.b64 p, [%0], %1;\n"
+        "@p bra WAIT_DONE;\n"
+        "bra WAIT_LOOP;\n"
+        "WAIT_DONE:\n"
+        "}\n" :: "r"(bar), "r"(parity) : "memory");
+}
+
+__device__ __forceinline__ void tma_load_2d(uint32_t dst, const CUtensorMap *tm, uint32_t c0, uint32_t c1, uint32_t bar)
+{
+    asm volatile("cp.async.bulk.tensor.2d.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1, {%2, %3}], [%4];"
+                 :: "r"(dst), "l"(tm), "r"(c0), "r"(c1), "r"(bar) : "memory");
+}
+
+__device__ __forceinline__ void tma_store_2d(const CUtensorMap *tm, uint32_t c0, uint32_t c1, uint32_t src)
+{
+    asm volatile("cp.async.bulk.tensor.2d.global.shared::cta.bulk_group [%0, {%1, %2}], [%3];"
+                 :: "l"(tm), "r"(c0), "r"(c1), "r"(src) : "memory");
+    asm volatile("cp.async.bulk.commit_group;" ::: "memory");
+}
+
+__device__ __forceinline__ void tma_store_wait_read()
+{
+    asm volatile("cp.async.bulk.wait_group.read 0;" ::: "memory");
+}
+
+__device__ __forceinline__ void tma_store_wait_all()
+{
+    asm volatile("cp.async.bulk.wait_group 0;" ::: "memory");
+}
+
+__device__ __forceinline__ uint4 lds128(uint32_t a)
+{
+    uint4 v;
+    asm volatile("ld.shared.v4.u32 {%0,%1,%2,%3}, [%4];" : "=r"(v.x), "=r"(v.y), "=r"(v.z), "=r"(v.w) : "r"(a) : "memory");
+    return v;
+}
+
+__device__ __forceinline__ void sts128(uint32_t a, uint4 v)
+{
+    asm volatile("st.shared.v4.u32 [%0], {%1,%2,%3,%4};" :: "r"(a), "r"(v.x), "r"(v.y), "r"(v.z), "r"(v.w) : "memory");
+}
+
+typedef CUresult (*EncodeTiledFn)(CUtensorMap *, CUtensorMapDataType, cuuint32_t, void *, const cuuint64_t *,
+                                  const cuuint64_t *, const cuuint32_t *, const cuuint32_t *, CUtensorMapInterleave,
+                                  CUtensorMapSwizzle, CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
+
+int make_row_tensor_map(CUtensorMap *tm, const void *ptr, uint64_t n_rows, uint64_t row_bytes)
+{
+    static EncodeTiledFn encode = nullptr;
+    if (!encode) {
+        void *fn = nullptr;
+        cudaDriverEntryPointQueryResult q;
+        BC_CUDA(cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &fn, cudaEnableDefault, &q), "cudaGetDriverEntryPoint");
+        if (!fn || q != cudaDriverEntryPointSuccess) { bc_set_error("cuTensorMapEncodeTiled is not available"); return BC_ERR_CUDA; }
+        encode = (EncodeTiledFn)fn;
+    }
+    const cuuint64_t dims[2] = { (cuuint64_t)row_bytes, (cuuint64_t)n_rows };
+    const cuuint64_t strides[1] = { (cuuint64_t)row_bytes };
+    const cuuint32_t box[2] = { (cuuint32_t)kSlab, 32u };
+    const cuuint32_t estr[2] = { 1u, 1u };
+    CUresult r = encode(tm, CU_TENSOR_MAP_DATA_TYPE_UINT8, 2, const_cast<void *>(ptr), dims, strides, box, estr,
+                        CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_64B, CU_TENSOR_MAP_L2_PROMOTION_NONE,
+                        CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+    if (r != CUDA_SUCCESS) { bc_set_error("cuTensorMapEncodeTiled failed (CUresult %d)", (int)r); return BC_ERR_CUDA; }
+    return BC_OK;
+}
+
+}  // namespace
+
+#endif
