@@ -24,8 +24,14 @@
 #include "../csrc/bc_internal.h"
 
 #define BC_MAX_DEVICES 16
-#define BC_SLOTS       3
-#define BC_CHUNK_BYTES ((size_t)32 << 20)   /* pipeline granule; a multiple of 4 KiB */
+#define BC_MAX_SLOTS   8
+/* Pipeline shape: `g_slots` chunks in flight, each `g_chunk` bytes (a multiple of 4 KiB).
+ * Defaults were picked on a B200 / PCIe Gen5 box (tools/pcie_probe.py);
+ * BULKCIPHER_CHUNK_MIB and BULKCIPHER_SLOTS override them before the first call. */
+static size_t g_chunk = (size_t)32 << 20;
+static int    g_slots = 3;
+#define BC_SLOTS       g_slots
+#define BC_CHUNK_BYTES g_chunk
 #define BC_MAX_SCRATCH 8
 
 /* ------------------------------------------------------------ error slot */
@@ -74,7 +80,7 @@ typedef struct {
     pthread_mutex_t scratch_lock;
     int        ready;
     int        sm_count;
-    bc_slot    slot[BC_SLOTS];
+    bc_slot    slot[BC_MAX_SLOTS];
     bc_scratch scratch[BC_MAX_SCRATCH];
     unsigned char *d_aux;       /* small device buffer: ivs, keys, contexts, last keystream */
     size_t     aux_cap;
@@ -85,6 +91,10 @@ static pthread_once_t g_once = PTHREAD_ONCE_INIT;
 
 static void init_locks(void)
 {
+    const char *e = getenv("BULKCIPHER_CHUNK_MIB");
+    if (e && atoi(e) >= 1 && atoi(e) <= 1024) g_chunk = (size_t)atoi(e) << 20;
+    e = getenv("BULKCIPHER_SLOTS");
+    if (e && atoi(e) >= 2 && atoi(e) <= BC_MAX_SLOTS) g_slots = atoi(e);
     for (int i = 0; i < BC_MAX_DEVICES; i++) {
         pthread_mutex_init(&g_dev[i].lock, NULL);
         pthread_mutex_init(&g_dev[i].scratch_lock, NULL);
