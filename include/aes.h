@@ -53,6 +53,12 @@ int aes_crypt_ecb(aes_context *ctx, int mode, const unsigned char input[16], uns
 int aes_crypt_cbc(aes_context *ctx, int mode, size_t length, unsigned char iv[16],
                   const unsigned char *input, unsigned char *output);
 
+/* aes-modes/aes.h:124 / aes.c:822-862 (the reference declares it but compiles it out).
+ * Byte-granular and resumable through *iv_off; ctx holds the ENCRYPT schedule for
+ * both directions.  Decrypt is block-parallel on the GPU, encrypt one serial chain. */
+int aes_crypt_cfb128(aes_context *ctx, int mode, size_t length, int *iv_off, unsigned char iv[16],
+                     const unsigned char *input, unsigned char *output);
+
 /* aes-modes/aes.c:869-900.  Byte-granular, resumable through *nc_off /
  * nonce_counter / stream_block, 128-bit big-endian counter increment. */
 int aes_crypt_ctr(aes_context *ctx, int length, int *nc_off, unsigned char nonce_counter[16],

@@ -121,6 +121,18 @@ int bc_aes_cbc_encrypt_batch_dev(const uint32_t *rk, int nr, size_t n_msgs, size
                                  const void *d_ivs, void *d_ivs_out,
                                  const void *d_in, void *d_out, void *stream);
 
+/* CFB128, the mode aes-modes/aes.h:124 declares and aes.c:822-862 implements behind
+ * POLARSSL_CIPHER_MODE_CFB (off in the reference build).  Whole blocks; rk is the
+ * ENCRYPTION schedule in both directions (aes.c:835,849).  Decrypt is parallel:
+ * P_i = E(C_{i-1}) ^ C_i, same chaining/scratch rules as bc_aes_cbc_decrypt_dev.
+ * Encrypt is serial per message, C_i = E(C_{i-1}) ^ P_i, batched across messages
+ * like bc_aes_cbc_encrypt_batch_dev. */
+int bc_aes_cfb128_decrypt_dev(const uint32_t *rk, int nr, const unsigned char iv[16],
+                              const void *d_in, void *d_out, size_t nbytes, void *stream);
+int bc_aes_cfb128_encrypt_batch_dev(const uint32_t *rk, int nr, size_t n_msgs, size_t msg_len,
+                                    const void *d_ivs, void *d_ivs_out,
+                                    const void *d_in, void *d_out, void *stream);
+
 /* ---- RC4 / ARC4 on device-resident buffers ------------------------------- */
 
 /* n_streams independent RC4 streams, stream-major contiguous: for stream s,
@@ -152,6 +164,10 @@ int bc_aes_cbc_decrypt_host(const uint32_t *rk, int nr, const unsigned char iv[1
                             const void *in, void *out, size_t nbytes);
 int bc_aes_cbc_encrypt_batch_host(const uint32_t *rk, int nr, size_t n_msgs, size_t msg_len,
                                   const void *ivs, void *ivs_out, const void *in, void *out);
+int bc_aes_cfb128_decrypt_host(const uint32_t *rk, int nr, const unsigned char iv[16],
+                               const void *in, void *out, size_t nbytes);
+int bc_aes_cfb128_encrypt_batch_host(const uint32_t *rk, int nr, size_t n_msgs, size_t msg_len,
+                                     const void *ivs, void *ivs_out, const void *in, void *out);
 /* in == NULL (here and in bc_arc4_batch_dev): write the raw keystream, which is
  * what arc4_prep produces (arc4.c:72-97).  length == 0 with ctx_out: key setup only. */
 int bc_arc4_batch_host(size_t n_streams, const void *keys, unsigned keylen, size_t length,

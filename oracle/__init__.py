@@ -143,6 +143,17 @@ class Oracle:
         self.lib.orc_aes_ctr(C.byref(k), d.size, C.byref(off), _p(nc), _p(sb), _p(d), _p(out))
         return out, off.value, nc.tobytes(), sb.tobytes()
 
+    def aes_cfb128(self, key: bytes, mode: int, iv: bytes, data, iv_off: int = 0):
+        d = _u8(data)
+        out = np.empty_like(d)
+        ivb = np.array(_u8(iv))
+        off = C.c_int(iv_off)
+        k = self._key(key, ENC)
+        self.lib.orc_aes_cfb128.argtypes = [C.c_void_p, C.c_int, C.c_size_t, C.POINTER(C.c_int), C.c_void_p,
+                                            C.c_void_p, C.c_void_p]
+        self.lib.orc_aes_cfb128(C.byref(k), mode, d.size, C.byref(off), _p(ivb), _p(d), _p(out))
+        return out, off.value, ivb.tobytes()
+
     def aes_cbc_encrypt_batch(self, key: bytes, ivs, data, msg_len: int):
         d = _u8(data)
         out = np.empty_like(d)
@@ -306,6 +317,16 @@ class Ref:
         off = C.c_int(nc_off)
         self.lib.ref_aes_ctr_bulk(self._ctx(key, ENC), d.size, C.byref(off), _p(nc), _p(sb), _p(d), _p(out))
         return out, off.value, nc.tobytes(), sb.tobytes()
+
+    def aes_cfb128(self, key: bytes, mode: int, iv: bytes, data, iv_off: int = 0):
+        d = _u8(data)
+        out = np.empty_like(d)
+        ivb = np.array(_u8(iv))
+        off = C.c_int(iv_off)
+        self.lib.ref_aes_crypt_cfb128.argtypes = [C.c_void_p, C.c_int, C.c_size_t, C.POINTER(C.c_int), C.c_void_p,
+                                                  C.c_void_p, C.c_void_p]
+        self.lib.ref_aes_crypt_cfb128(self._ctx(key, ENC), mode, d.size, C.byref(off), _p(ivb), _p(d), _p(out))
+        return out, off.value, ivb.tobytes()
 
     def aes_cbc_encrypt_batch(self, key: bytes, ivs, data, msg_len: int):
         d = _u8(data)

@@ -217,6 +217,29 @@ int orc_aes_ctr(const orc_aes_key *k, size_t length, int *nc_off, uint8_t nonce_
     return 0;
 }
 
+/* aes_crypt_cfb128, aes.c:822-862 (compiled out of the reference build because
+ * POLARSSL_CIPHER_MODE_CFB is undefined, but declared at aes.h:124 and covered by
+ * the SP 800-38A vectors at aes.c:958-1015).  Byte-granular; iv doubles as the
+ * keystream block, *iv_off is the position inside it; always the ENCRYPT schedule. */
+int orc_aes_cfb128(const orc_aes_key *k, int mode, size_t length, int *iv_off, uint8_t iv[16],
+                   const uint8_t *in, uint8_t *out)
+{
+    int n = *iv_off;
+    for (size_t p = 0; p < length; p++) {
+        if (n == 0) orc_aes_ecb_block(k, ORC_ENCRYPT, iv, iv);
+        if (mode == ORC_DECRYPT) {
+            uint8_t c = in[p];
+            out[p] = c ^ iv[n];
+            iv[n] = c;
+        } else {
+            iv[n] = out[p] = iv[n] ^ in[p];
+        }
+        n = (n + 1) & 15;
+    }
+    *iv_off = n;
+    return 0;
+}
+
 /* ------------------------------------------------------------ aesni.h calls */
 
 /* Packed schedule = 16 bytes per round key, i.e. the LE words back to back

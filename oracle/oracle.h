@@ -48,6 +48,9 @@ int  orc_aes_cbc(const orc_aes_key *k, int mode, size_t length, uint8_t iv[16],
 int  orc_aes_ctr(const orc_aes_key *k, size_t length, int *nc_off, uint8_t nonce_counter[16],
                  uint8_t stream_block[16], const uint8_t *in, uint8_t *out);
 
+int  orc_aes_cfb128(const orc_aes_key *k, int mode, size_t length, int *iv_off, uint8_t iv[16],
+                    const uint8_t *in, uint8_t *out);
+
 /* aesni.h-style calls on a packed schedule (16 bytes per round key). */
 void orc_aesni_key256(const uint8_t *userkey, uint8_t *sched /*240 B*/);
 void orc_aesni_pack(const orc_aes_key *k, uint8_t *sched /*16*(nr+1) B*/);

@@ -32,7 +32,8 @@ BC_OK, BC_ERR_CUDA, BC_ERR_BAD_ARG, BC_ERR_NO_DEVICE, BC_ERR_OVERLAP, BC_ERR_TOO
 
 # every symbol include/*.h declares (tests check the library exports all of them)
 DROPIN_SYMBOLS = [
-    "aes_setkey_enc", "aes_setkey_dec", "aes_crypt_ecb", "aes_crypt_cbc", "aes_crypt_ctr", "aes_self_test",
+    "aes_setkey_enc", "aes_setkey_dec", "aes_crypt_ecb", "aes_crypt_cbc", "aes_crypt_ctr", "aes_crypt_cfb128",
+    "aes_self_test",
     "CheckAESSupport", "AES_256_Key_Expansion", "AES_128_Key_Expansion", "AES_192_Key_Expansion",
     "AES_ECB_encrypt", "AES_ECB_decrypt", "AES_CTR_encrypt",
     "arc4_setup", "arc4_prep", "arc4_crypt", "arc4_self_test", "rc4_init", "rc4_crypt",
@@ -43,6 +44,8 @@ BC_SYMBOLS = [
     "bc_device_sync",
     "bc_aes_ctr_dev", "bc_aes_ecb_dev", "bc_aes_cbc_decrypt_dev", "bc_aes_cbc_encrypt_batch_dev",
     "bc_arc4_batch_dev", "bc_xor_dev", "bc_aes_cbc_decrypt_inplace_noalloc_dev",
+    "bc_aes_cfb128_decrypt_dev", "bc_aes_cfb128_encrypt_batch_dev", "bc_aes_cfb128_decrypt_host",
+    "bc_aes_cfb128_encrypt_batch_host",
     "bc_aes_ctr_host", "bc_aes_ecb_host", "bc_aes_cbc_decrypt_host", "bc_aes_cbc_encrypt_batch_host",
     "bc_arc4_batch_host", "bc_xor_host", "bc_aes_ctr_host_multi",
 ]
@@ -94,6 +97,11 @@ def lib() -> C.CDLL:
     L.bc_aes_cbc_decrypt_dev.argtypes = [vp, i32, vp, vp, vp, sz, vp]
     L.bc_aes_cbc_decrypt_inplace_noalloc_dev.argtypes = [vp, i32, vp, vp, sz, vp]
     L.bc_aes_cbc_encrypt_batch_dev.argtypes = [vp, i32, sz, sz, vp, vp, vp, vp, vp]
+    L.bc_aes_cfb128_decrypt_dev.argtypes = [vp, i32, vp, vp, vp, sz, vp]
+    L.bc_aes_cfb128_encrypt_batch_dev.argtypes = [vp, i32, sz, sz, vp, vp, vp, vp, vp]
+    L.bc_aes_cfb128_decrypt_host.argtypes = [vp, i32, vp, vp, vp, sz]
+    L.bc_aes_cfb128_encrypt_batch_host.argtypes = [vp, i32, sz, sz, vp, vp, vp, vp]
+    L.aes_crypt_cfb128.argtypes = [vp, i32, sz, C.POINTER(C.c_int), vp, vp, vp]
     L.bc_arc4_batch_dev.argtypes = [sz, vp, u32, sz, vp, vp, vp, vp, vp]
     L.bc_xor_dev.argtypes = [vp, vp, vp, sz, vp]
     L.bc_aes_ctr_host.argtypes = [vp, i32, vp, i32, u64, vp, vp, sz, vp]
@@ -187,6 +195,15 @@ def aes_crypt_ctr(ctx: aes_context, nonce_counter: bytes, data, nc_off: int = 0,
     off = C.c_int(nc_off)
     rc = lib().aes_crypt_ctr(C.byref(ctx), d.size, C.byref(off), _ptr(nc), _ptr(sb), _ptr(d), _ptr(o))
     return rc, o, off.value, nc.tobytes(), sb.tobytes()
+
+
+def aes_crypt_cfb128(ctx: aes_context, mode: int, iv: bytes, data, iv_off: int = 0, inplace: bool = False):
+    d = np.array(_u8(data))
+    o = d if inplace else np.empty_like(d)
+    ivb = np.array(_u8(iv))
+    off = C.c_int(iv_off)
+    rc = lib().aes_crypt_cfb128(C.byref(ctx), mode, d.size, C.byref(off), _ptr(ivb), _ptr(d), _ptr(o))
+    return rc, o, off.value, ivb.tobytes()
 
 
 # ------------------------------------------------------------- aesni.h face

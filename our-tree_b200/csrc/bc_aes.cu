@@ -396,7 +396,7 @@ aes_ctr_kernel(const __grid_constant__ AesSched ks, const __grid_constant__ CtrA
 
 /* --------------------------------------------------- ECB enc/dec, CBC dec */
 
-enum { MODE_ECB_ENC = 0, MODE_ECB_DEC = 1, MODE_CBC_DEC = 2 };
+enum { MODE_ECB_ENC = 0, MODE_ECB_DEC = 1, MODE_CBC_DEC = 2, MODE_CFB_DEC = 3 };
 
 struct BlkArgs {
     const uint4 *in;
@@ -411,7 +411,8 @@ template <int NR, int MODE>
 __global__ void __launch_bounds__(kThreads, 1)
 aes_blocks_kernel(const __grid_constant__ AesSched ks, const __grid_constant__ BlkArgs a)
 {
-    constexpr bool DEC = (MODE != MODE_ECB_ENC);
+    constexpr bool DEC = (MODE == MODE_ECB_DEC || MODE == MODE_CBC_DEC);      /* inverse tables */
+    constexpr bool CHAIN = (MODE == MODE_CBC_DEC || MODE == MODE_CFB_DEC);    /* needs C[i-1] */
     extern __shared__ __align__(1024) uint32_t smem[];
     fill_tables<DEC>(smem);
     __syncthreads();
@@ -426,8 +427,8 @@ aes_blocks_kernel(const __grid_constant__ AesSched ks, const __grid_constant__ B
     for (uint64_t g = warp_gid; g < a.n_groups; g += n_warps) {
         const uint64_t b0 = g * 256 + lane;
         const bool full = (g * 256 + 256 <= a.nblocks);
-        uint4 carry = make_uint4(0, 0, 0, 0);      /* CBC: lane 31's ciphertext of the previous row */
-        if (MODE == MODE_CBC_DEC) {
+        uint4 carry = make_uint4(0, 0, 0, 0);      /* chained modes: lane 31's ciphertext of the previous row */
+        if (CHAIN) {
             if (g == 0) carry = a.iv;
             else carry = a.boundary ? a.boundary[g] : a.in[g * 256 - 1];
         }
@@ -437,10 +438,8 @@ aes_blocks_kernel(const __grid_constant__ AesSched ks, const __grid_constant__ B
             const bool live = full || b < a.nblocks;
             uint4 c = make_uint4(0, 0, 0, 0);
             if (live) c = ld_stream(a.in + b);
-            State s = { c.x, c.y, c.z, c.w };
-            s = cipher_block<NR, DEC>(s, ks, tb);
-            if (MODE == MODE_CBC_DEC) {            /* P_i = D(C_i) ^ C_{i-1}  (aes.c:784-797) */
-                uint4 prev;
+            uint4 prev = make_uint4(0, 0, 0, 0);
+            if (CHAIN) {                           /* C_{i-1}: the lane to the left, lane 0 from the previous row */
                 prev.x = __shfl_up_sync(0xffffffffu, c.x, 1);
                 prev.y = __shfl_up_sync(0xffffffffu, c.y, 1);
                 prev.z = __shfl_up_sync(0xffffffffu, c.z, 1);
@@ -450,7 +449,15 @@ aes_blocks_kernel(const __grid_constant__ AesSched ks, const __grid_constant__ B
                 carry.y = __shfl_sync(0xffffffffu, c.y, 31);
                 carry.z = __shfl_sync(0xffffffffu, c.z, 31);
                 carry.w = __shfl_sync(0xffffffffu, c.w, 31);
+            }
+            State s;
+            if (MODE == MODE_CFB_DEC) s = State{ prev.x, prev.y, prev.z, prev.w };   /* P_i = E(C_{i-1}) ^ C_i (aes.c:832-842) */
+            else s = State{ c.x, c.y, c.z, c.w };
+            s = cipher_block<NR, DEC>(s, ks, tb);
+            if (MODE == MODE_CBC_DEC) {            /* P_i = D(C_i) ^ C_{i-1}  (aes.c:784-797) */
                 s.a ^= prev.x; s.b ^= prev.y; s.c ^= prev.z; s.d ^= prev.w;
+            } else if (MODE == MODE_CFB_DEC) {
+                s.a ^= c.x; s.b ^= c.y; s.c ^= c.z; s.d ^= c.w;
             }
             if (live) st_stream(a.out + b, make_uint4(s.a, s.b, s.c, s.d));
         }
@@ -478,7 +485,7 @@ struct CbcEncArgs {
 
 /* One thread per message: the chain C_i = E(P_i ^ C_{i-1}) (aes.c:801-812) is
  * serial inside a message and independent across messages. */
-template <int NR>
+template <int NR, bool CFB>
 __global__ void __launch_bounds__(kThreads, 1)
 aes_cbc_enc_batch_kernel(const __grid_constant__ AesSched ks, const __grid_constant__ CbcEncArgs a)
 {
@@ -494,24 +501,12 @@ aes_cbc_enc_batch_kernel(const __grid_constant__ AesSched ks, const __grid_const
         uint4 c = a.ivs[m];
         const uint4 *pi = a.in + m * a.blocks_per_msg;
         uint4 *po = a.out + m * a.blocks_per_msg;
-        /* two blocks (one 32-byte sector) per trip; the load of the next pair is independent of the chain */
-        uint64_t i = 0;
-        for (; i + 2 <= a.blocks_per_msg; i += 2) {
-            const uint4 p0 = pi[i], p1 = pi[i + 1];
-            State s = { p0.x ^ c.x, p0.y ^ c.y, p0.z ^ c.z, p0.w ^ c.w };
-            s = cipher_block<NR, false>(s, ks, tb);
-            const uint4 c0 = make_uint4(s.a, s.b, s.c, s.d);
-            State t = { p1.x ^ c0.x, p1.y ^ c0.y, p1.z ^ c0.z, p1.w ^ c0.w };
-            t = cipher_block<NR, false>(t, ks, tb);
-            c = make_uint4(t.a, t.b, t.c, t.d);
-            po[i] = c0;
-            po[i + 1] = c;
-        }
-        if (i < a.blocks_per_msg) {
+        /* CBC: C_i = E(P_i ^ C_{i-1}) (aes.c:801-812); CFB128: C_i = E(C_{i-1}) ^ P_i (aes.c:846-856) */
+        for (uint64_t i = 0; i < a.blocks_per_msg; i++) {
             const uint4 p0 = pi[i];
-            State s = { p0.x ^ c.x, p0.y ^ c.y, p0.z ^ c.z, p0.w ^ c.w };
+            State s = CFB ? State{ c.x, c.y, c.z, c.w } : State{ p0.x ^ c.x, p0.y ^ c.y, p0.z ^ c.z, p0.w ^ c.w };
             s = cipher_block<NR, false>(s, ks, tb);
-            c = make_uint4(s.a, s.b, s.c, s.d);
+            c = CFB ? make_uint4(s.a ^ p0.x, s.b ^ p0.y, s.c ^ p0.z, s.d ^ p0.w) : make_uint4(s.a, s.b, s.c, s.d);
             po[i] = c;
         }
         if (a.ivs_out) a.ivs_out[m] = c;     /* iv <- last ciphertext block (aes.c:807) */
@@ -524,7 +519,7 @@ aes_cbc_enc_batch_kernel(const __grid_constant__ AesSched ks, const __grid_const
  * lane walks its own message.  The chain value never leaves registers. */
 constexpr int kCbcTmaMaxWarps = 24;          /* 128 KB tables + 24 x 4 KB staging fits 227 KB */
 
-template <int NR>
+template <int NR, bool CFB>
 __global__ void __launch_bounds__(kCbcTmaMaxWarps * 32, 1)
 aes_cbc_enc_batch_tma_kernel(const __grid_constant__ AesSched ks, const __grid_constant__ CbcEncArgs a,
                              const __grid_constant__ CUtensorMap tm_in, const __grid_constant__ CUtensorMap tm_out)
@@ -573,9 +568,10 @@ aes_cbc_enc_batch_tma_kernel(const __grid_constant__ AesSched ks, const __grid_c
                 if (q * 16 < valid) {
                     const uint32_t sa = sbuf + box_chunk_off(lane, q);
                     const uint4 pt = lds128(sa);
-                    State s = { pt.x ^ c.x, pt.y ^ c.y, pt.z ^ c.z, pt.w ^ c.w };    /* aes.c:803-804 */
+                    State s = CFB ? State{ c.x, c.y, c.z, c.w }
+                                  : State{ pt.x ^ c.x, pt.y ^ c.y, pt.z ^ c.z, pt.w ^ c.w };    /* aes.c:803-804 / :849-853 */
                     s = cipher_block<NR, false>(s, ks, tb);
-                    c = make_uint4(s.a, s.b, s.c, s.d);
+                    c = CFB ? make_uint4(s.a ^ pt.x, s.b ^ pt.y, s.c ^ pt.z, s.d ^ pt.w) : make_uint4(s.a, s.b, s.c, s.d);
                     sts128(sa, c);
                 }
             }
@@ -665,7 +661,7 @@ int launch_ctr(const AesSched &ks, const CtrArgs &a, cudaStream_t st)
 template <int NR, int MODE>
 int launch_blocks(const AesSched &ks, const BlkArgs &a, cudaStream_t st)
 {
-    constexpr int smem = (MODE == MODE_ECB_ENC) ? kEncSmemBytes : kDecSmemBytes;
+    constexpr int smem = (MODE == MODE_ECB_ENC || MODE == MODE_CFB_DEC) ? kEncSmemBytes : kDecSmemBytes;
     int rc = set_smem(aes_blocks_kernel<NR, MODE>, smem);
     if (rc) return rc;
     int grid = grid_for(a.n_groups);
@@ -685,7 +681,7 @@ int launch_blocks_nr(int nr, const AesSched &ks, const BlkArgs &a, cudaStream_t 
     }
 }
 
-template <int NR>
+template <int NR, bool CFB>
 int launch_cbc_enc(const AesSched &ks, const CbcEncArgs &a, cudaStream_t st)
 {
     const int sms = bc_cached_sm_count();
@@ -704,12 +700,12 @@ int launch_cbc_enc(const AesSched &ks, const CbcEncArgs &a, cudaStream_t st)
         int rc = make_row_tensor_map(&tin, a.in, a.n_msgs, msg_len);
         if (rc) return rc;
         if ((rc = make_row_tensor_map(&tout, a.out, a.n_msgs, msg_len))) return rc;
-        if ((rc = set_smem(aes_cbc_enc_batch_tma_kernel<NR>, kEncSmemBytes + kCbcTmaMaxWarps * (2 * kBoxBytes + 16)))) return rc;
-        aes_cbc_enc_batch_tma_kernel<NR><<<grid, (int)warps * 32, smem, st>>>(ks, a, tin, tout);
+        if ((rc = set_smem(aes_cbc_enc_batch_tma_kernel<NR, CFB>, kEncSmemBytes + kCbcTmaMaxWarps * (2 * kBoxBytes + 16)))) return rc;
+        aes_cbc_enc_batch_tma_kernel<NR, CFB><<<grid, (int)warps * 32, smem, st>>>(ks, a, tin, tout);
         BC_CUDA(cudaGetLastError(), "aes_cbc_enc_batch_tma_kernel launch");
         return BC_OK;
     }
-    int rc = set_smem(aes_cbc_enc_batch_kernel<NR>, kEncSmemBytes);
+    int rc = set_smem(aes_cbc_enc_batch_kernel<NR, CFB>, kEncSmemBytes);
     if (rc) return rc;
     /* spread the messages evenly: ceil(n/SMs) threads per CTA, whole warps, <= kThreads */
     uint64_t per = (a.n_msgs + sms - 1) / sms;
@@ -717,7 +713,7 @@ int launch_cbc_enc(const AesSched &ks, const CbcEncArgs &a, cudaStream_t st)
     if (per > kThreads) per = kThreads;
     uint64_t ctas = (a.n_msgs + per - 1) / per;
     int grid = (int)(ctas < (uint64_t)sms ? ctas : (uint64_t)sms);
-    aes_cbc_enc_batch_kernel<NR><<<grid, (int)per, kEncSmemBytes, st>>>(ks, a);
+    aes_cbc_enc_batch_kernel<NR, CFB><<<grid, (int)per, kEncSmemBytes, st>>>(ks, a);
     BC_CUDA(cudaGetLastError(), "aes_cbc_enc_batch_kernel launch");
     return BC_OK;
 }
@@ -797,13 +793,17 @@ extern "C" int bc_aes_ecb_dev(const uint32_t *rk, int nr, int mode, const void *
                               : launch_blocks_nr<MODE_ECB_DEC>(nr, ks, a, st);
 }
 
-extern "C" int bc_aes_cbc_decrypt_dev(const uint32_t *rk, int nr, const unsigned char iv[16],
-                                      const void *d_in, void *d_out, size_t nbytes, void *stream)
+namespace {
+
+/* shared body of the two block-parallel chained decrypts (CBC, CFB128) */
+template <int MODE>
+int chained_decrypt_dev(const uint32_t *rk, int nr, const unsigned char iv[16],
+                        const void *d_in, void *d_out, size_t nbytes, void *stream, const char *what)
 {
     int rc = check_common(rk, nr, d_in, d_out, nbytes);
     if (rc) return rc;
     if (!iv) { bc_set_error("iv is NULL"); return BC_ERR_BAD_ARG; }
-    if (nbytes % 16) { bc_set_error("CBC length %zu is not a multiple of 16", nbytes); return BC_ERR_BAD_ARG; }
+    if (nbytes % 16) { bc_set_error("%s length %zu is not a multiple of 16", what, nbytes); return BC_ERR_BAD_ARG; }
     if ((rc = check_overlap(d_in, d_out, nbytes))) return rc;
     if (nbytes == 0) return BC_OK;
     AesSched ks;
@@ -830,16 +830,16 @@ extern "C" int bc_aes_cbc_decrypt_dev(const uint32_t *rk, int nr, const unsigned
         BC_CUDA(cudaGetLastError(), "cbc_save_boundaries_kernel launch");
         a.boundary = (const uint4 *)scratch;
     }
-    return launch_blocks_nr<MODE_CBC_DEC>(nr, ks, a, st);
+    return launch_blocks_nr<MODE>(nr, ks, a, st);
 }
 
-extern "C" int bc_aes_cbc_encrypt_batch_dev(const uint32_t *rk, int nr, size_t n_msgs, size_t msg_len,
-                                            const void *d_ivs, void *d_ivs_out,
-                                            const void *d_in, void *d_out, void *stream)
+template <bool CFB>
+int chained_encrypt_batch_dev(const uint32_t *rk, int nr, size_t n_msgs, size_t msg_len,
+                              const void *d_ivs, void *d_ivs_out, const void *d_in, void *d_out, void *stream)
 {
     int rc = check_common(rk, nr, d_in, d_out, n_msgs * msg_len);
     if (rc) return rc;
-    if (msg_len % 16) { bc_set_error("CBC message length %zu is not a multiple of 16", msg_len); return BC_ERR_BAD_ARG; }
+    if (msg_len % 16) { bc_set_error("message length %zu is not a multiple of 16", msg_len); return BC_ERR_BAD_ARG; }
     if (n_msgs == 0 || msg_len == 0) return BC_OK;
     if (!d_ivs || ((uintptr_t)d_ivs & 15u) || ((uintptr_t)d_ivs_out & 15u)) {
         bc_set_error("d_ivs must be non-NULL and 16-byte aligned");
@@ -857,10 +857,38 @@ extern "C" int bc_aes_cbc_encrypt_batch_dev(const uint32_t *rk, int nr, size_t n
     a.blocks_per_msg = msg_len / 16;
     cudaStream_t st = (cudaStream_t)stream;
     switch (nr) {
-    case 10: return launch_cbc_enc<10>(ks, a, st);
-    case 12: return launch_cbc_enc<12>(ks, a, st);
-    default: return launch_cbc_enc<14>(ks, a, st);
+    case 10: return launch_cbc_enc<10, CFB>(ks, a, st);
+    case 12: return launch_cbc_enc<12, CFB>(ks, a, st);
+    default: return launch_cbc_enc<14, CFB>(ks, a, st);
     }
+}
+
+}  // namespace
+
+extern "C" int bc_aes_cbc_decrypt_dev(const uint32_t *rk, int nr, const unsigned char iv[16],
+                                      const void *d_in, void *d_out, size_t nbytes, void *stream)
+{
+    return chained_decrypt_dev<MODE_CBC_DEC>(rk, nr, iv, d_in, d_out, nbytes, stream, "CBC");
+}
+
+extern "C" int bc_aes_cfb128_decrypt_dev(const uint32_t *rk, int nr, const unsigned char iv[16],
+                                         const void *d_in, void *d_out, size_t nbytes, void *stream)
+{
+    return chained_decrypt_dev<MODE_CFB_DEC>(rk, nr, iv, d_in, d_out, nbytes, stream, "CFB128");
+}
+
+extern "C" int bc_aes_cbc_encrypt_batch_dev(const uint32_t *rk, int nr, size_t n_msgs, size_t msg_len,
+                                            const void *d_ivs, void *d_ivs_out,
+                                            const void *d_in, void *d_out, void *stream)
+{
+    return chained_encrypt_batch_dev<false>(rk, nr, n_msgs, msg_len, d_ivs, d_ivs_out, d_in, d_out, stream);
+}
+
+extern "C" int bc_aes_cfb128_encrypt_batch_dev(const uint32_t *rk, int nr, size_t n_msgs, size_t msg_len,
+                                               const void *d_ivs, void *d_ivs_out,
+                                               const void *d_in, void *d_out, void *stream)
+{
+    return chained_encrypt_batch_dev<true>(rk, nr, n_msgs, msg_len, d_ivs, d_ivs_out, d_in, d_out, stream);
 }
 
 /* ------------------------------------------------ allocation-free variant */

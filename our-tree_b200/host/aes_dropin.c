@@ -133,6 +133,50 @@ int aes_crypt_cbc(aes_context *ctx, int mode, size_t length, unsigned char iv[16
     return bc_aes_cbc_encrypt_batch_host(rk, ctx->nr, 1, length, iv, iv, input, output);
 }
 
+/* aes.c:822-862.  The bytes that finish a block begun by an earlier call and the
+ * bytes of a trailing partial block are plain XORs with a keystream block the GPU
+ * produced (E(iv) in place, aes.c:835,849); all whole blocks run as one GPU call. */
+int aes_crypt_cfb128(aes_context *ctx, int mode, size_t length, int *iv_off, unsigned char iv[16],
+                     const unsigned char *input, unsigned char *output)
+{
+    if (!iv_off || !iv) { bc_set_error("aes_crypt_cfb128: NULL iv/iv_off"); return BC_ERR_BAD_ARG; }
+    uint32_t rk[60];
+    int rc = ctx_load(ctx, rk);
+    if (rc) return rc;
+    int n = *iv_off & 15;
+    /* 1. finish the keystream block the caller carried in */
+    while (n != 0 && length > 0) {
+        if (mode == AES_DECRYPT) { unsigned char c = *input++; *output++ = (unsigned char)(c ^ iv[n]); iv[n] = c; }
+        else iv[n] = *output++ = (unsigned char)(iv[n] ^ *input++);
+        n = (n + 1) & 15;
+        length--;
+    }
+    /* 2. whole blocks */
+    const size_t whole = length & ~(size_t)15;
+    if (whole) {
+        if (mode == AES_DECRYPT) {
+            unsigned char last[16];
+            memcpy(last, input + whole - 16, 16);                 /* before an in-place overwrite */
+            if ((rc = bc_aes_cfb128_decrypt_host(rk, ctx->nr, iv, input, output, whole))) return rc;
+            memcpy(iv, last, 16);
+        } else if ((rc = bc_aes_cfb128_encrypt_batch_host(rk, ctx->nr, 1, whole, iv, iv, input, output))) {
+            return rc;
+        }
+        input += whole; output += whole; length -= whole;
+    }
+    /* 3. a trailing partial block: iv <- E(iv), then byte-wise */
+    if (length) {
+        if ((rc = bc_aes_ecb_host(rk, ctx->nr, BC_ENCRYPT, iv, iv, 16))) return rc;
+        while (length--) {
+            if (mode == AES_DECRYPT) { unsigned char c = *input++; *output++ = (unsigned char)(c ^ iv[n]); iv[n] = c; }
+            else iv[n] = *output++ = (unsigned char)(iv[n] ^ *input++);
+            n = (n + 1) & 15;
+        }
+    }
+    *iv_off = n;
+    return 0;
+}
+
 int aes_crypt_ctr(aes_context *ctx, int length, int *nc_off, unsigned char nonce_counter[16],
                   unsigned char stream_block[16], const unsigned char *input, unsigned char *output)
 {

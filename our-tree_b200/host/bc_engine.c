@@ -421,27 +421,27 @@ int bc_aes_ecb_host(const uint32_t *rk, int nr, int mode, const void *in, void *
 
 /* ------------------------------------------------------ AES-CBC decrypt */
 
-typedef struct { const uint32_t *rk; int nr; const unsigned char *ivs; } cbcd_op;
+typedef struct { const uint32_t *rk; int nr; const unsigned char *ivs; int cfb; } cbcd_op;
 
 static int cbcd_chunk(void *arg, size_t idx, size_t off, size_t n, void *d, cudaStream_t st)
 {
     cbcd_op *o = (cbcd_op *)arg;
     (void)off;
-    return bc_aes_cbc_decrypt_dev(o->rk, o->nr, o->ivs + 16 * idx, d, d, n, st);
+    return (o->cfb ? bc_aes_cfb128_decrypt_dev : bc_aes_cbc_decrypt_dev)(o->rk, o->nr, o->ivs + 16 * idx, d, d, n, st);
 }
 
-int bc_aes_cbc_decrypt_host(const uint32_t *rk, int nr, const unsigned char iv[16],
-                            const void *in, void *out, size_t nbytes)
+static int chained_decrypt_host(int cfb, const uint32_t *rk, int nr, const unsigned char iv[16],
+                                const void *in, void *out, size_t nbytes)
 {
     int rc = check_host_args(rk, nr, in, out, nbytes);
     if (rc) return rc;
     if (!iv) { bc_set_error("iv is NULL"); return BC_ERR_BAD_ARG; }
-    if (nbytes % 16) { bc_set_error("CBC length %zu is not a multiple of 16", nbytes); return BC_ERR_BAD_ARG; }
+    if (nbytes % 16) { bc_set_error("%s length %zu is not a multiple of 16", cfb ? "CFB128" : "CBC", nbytes); return BC_ERR_BAD_ARG; }
     if (nbytes == 0) return BC_OK;
     bc_dev *d;
     if ((rc = dev_prepare(&d))) return rc;
     if (classify(in) == 2 && classify(out) == 2) {
-        rc = bc_aes_cbc_decrypt_dev(rk, nr, iv, in, out, nbytes, NULL);
+        rc = (cfb ? bc_aes_cfb128_decrypt_dev : bc_aes_cbc_decrypt_dev)(rk, nr, iv, in, out, nbytes, NULL);
         return rc ? rc : bc_device_sync();
     }
     /* Chunk k chains from the last ciphertext block of chunk k-1.  Collect those
@@ -453,7 +453,7 @@ int bc_aes_cbc_decrypt_host(const uint32_t *rk, int nr, const unsigned char iv[1
     for (size_t k = 1; k < n_chunks; k++) memcpy(ivs + 16 * k, (const unsigned char *)in + k * BC_CHUNK_BYTES - 16, 16);
     pthread_mutex_lock(&d->lock);
     if ((rc = dev_ensure_slots(d)) == BC_OK) {
-        cbcd_op o = { rk, nr, ivs };
+        cbcd_op o = { rk, nr, ivs, cfb };
         rc = run_pipeline(d, (const unsigned char *)in, (unsigned char *)out, nbytes, BC_CHUNK_BYTES, cbcd_chunk, &o);
     }
     pthread_mutex_unlock(&d->lock);
@@ -461,12 +461,24 @@ int bc_aes_cbc_decrypt_host(const uint32_t *rk, int nr, const unsigned char iv[1
     return rc;
 }
 
+int bc_aes_cbc_decrypt_host(const uint32_t *rk, int nr, const unsigned char iv[16],
+                            const void *in, void *out, size_t nbytes)
+{
+    return chained_decrypt_host(0, rk, nr, iv, in, out, nbytes);
+}
+
+int bc_aes_cfb128_decrypt_host(const uint32_t *rk, int nr, const unsigned char iv[16],
+                               const void *in, void *out, size_t nbytes)
+{
+    return chained_decrypt_host(1, rk, nr, iv, in, out, nbytes);
+}
+
 /* ------------------------------------------- AES-CBC encrypt, batched msgs */
 
 typedef struct {
     const uint32_t *rk; int nr; size_t msg_len; size_t msgs_per_chunk;
     const unsigned char *ivs; unsigned char *ivs_out; unsigned char *d_ivs;   /* [BC_SLOTS][msgs_per_chunk][16] */
-    size_t n_msgs;
+    size_t n_msgs; int cfb;
 } cbce_op;
 
 static int cbce_chunk(void *arg, size_t idx, size_t off, size_t n, void *d, cudaStream_t st)
@@ -475,32 +487,33 @@ static int cbce_chunk(void *arg, size_t idx, size_t off, size_t n, void *d, cuda
     const size_t m0 = off / o->msg_len, nm = n / o->msg_len;
     unsigned char *d_iv = o->d_ivs + (idx % BC_SLOTS) * o->msgs_per_chunk * 16;
     BC_CUDA(cudaMemcpyAsync(d_iv, o->ivs + 16 * m0, 16 * nm, cudaMemcpyHostToDevice, st), "cudaMemcpyAsync ivs");
-    int rc = bc_aes_cbc_encrypt_batch_dev(o->rk, o->nr, nm, o->msg_len, d_iv, o->ivs_out ? d_iv : NULL, d, d, st);
+    int rc = (o->cfb ? bc_aes_cfb128_encrypt_batch_dev : bc_aes_cbc_encrypt_batch_dev)(
+        o->rk, o->nr, nm, o->msg_len, d_iv, o->ivs_out ? d_iv : NULL, d, d, st);
     if (rc) return rc;
     if (o->ivs_out)
         BC_CUDA(cudaMemcpyAsync(o->ivs_out + 16 * m0, d_iv, 16 * nm, cudaMemcpyDeviceToHost, st), "cudaMemcpyAsync ivs_out");
     return BC_OK;
 }
 
-int bc_aes_cbc_encrypt_batch_host(const uint32_t *rk, int nr, size_t n_msgs, size_t msg_len,
-                                  const void *ivs, void *ivs_out, const void *in, void *out)
+static int chained_encrypt_batch_host(int cfb, const uint32_t *rk, int nr, size_t n_msgs, size_t msg_len,
+                                      const void *ivs, void *ivs_out, const void *in, void *out)
 {
     int rc = check_host_args(rk, nr, in, out, n_msgs * msg_len);
     if (rc) return rc;
-    if (msg_len % 16) { bc_set_error("CBC message length %zu is not a multiple of 16", msg_len); return BC_ERR_BAD_ARG; }
+    if (msg_len % 16) { bc_set_error("message length %zu is not a multiple of 16", msg_len); return BC_ERR_BAD_ARG; }
     if (n_msgs == 0 || msg_len == 0) return BC_OK;
     if (!ivs) { bc_set_error("ivs is NULL"); return BC_ERR_BAD_ARG; }
     bc_dev *d;
     if ((rc = dev_prepare(&d))) return rc;
     if (classify(in) == 2 && classify(out) == 2 && classify(ivs) == 2) {
-        rc = bc_aes_cbc_encrypt_batch_dev(rk, nr, n_msgs, msg_len, ivs, ivs_out, in, out, NULL);
+        rc = (cfb ? bc_aes_cfb128_encrypt_batch_dev : bc_aes_cbc_encrypt_batch_dev)(rk, nr, n_msgs, msg_len, ivs, ivs_out, in, out, NULL);
         return rc ? rc : bc_device_sync();
     }
     pthread_mutex_lock(&d->lock);
     if ((rc = dev_ensure_slots(d)) == BC_OK) {
         if (msg_len <= BC_CHUNK_BYTES) {
             cbce_op o = { rk, nr, msg_len, BC_CHUNK_BYTES / msg_len, (const unsigned char *)ivs,
-                          (unsigned char *)ivs_out, NULL, n_msgs };
+                          (unsigned char *)ivs_out, NULL, n_msgs, cfb };
             if ((rc = dev_ensure_aux(d, BC_SLOTS * o.msgs_per_chunk * 16)) == BC_OK) {
                 o.d_ivs = d->d_aux;
                 rc = run_pipeline(d, (const unsigned char *)in, (unsigned char *)out, n_msgs * msg_len,
@@ -514,7 +527,7 @@ int bc_aes_cbc_encrypt_batch_host(const uint32_t *rk, int nr, size_t n_msgs, siz
                 memcpy(iv, (const unsigned char *)ivs + 16 * m, 16);
                 for (size_t off = 0; off < msg_len && rc == BC_OK; off += BC_CHUNK_BYTES) {
                     size_t n = msg_len - off < BC_CHUNK_BYTES ? msg_len - off : BC_CHUNK_BYTES;
-                    cbce_op o = { rk, nr, n, 1, iv, iv, NULL, 1 };
+                    cbce_op o = { rk, nr, n, 1, iv, iv, NULL, 1, cfb };
                     if ((rc = dev_ensure_aux(d, BC_SLOTS * 16)) != BC_OK) break;
                     o.d_ivs = d->d_aux;
                     rc = run_pipeline(d, (const unsigned char *)in + m * msg_len + off,
@@ -526,6 +539,18 @@ int bc_aes_cbc_encrypt_batch_host(const uint32_t *rk, int nr, size_t n_msgs, siz
     }
     pthread_mutex_unlock(&d->lock);
     return rc;
+}
+
+int bc_aes_cbc_encrypt_batch_host(const uint32_t *rk, int nr, size_t n_msgs, size_t msg_len,
+                                  const void *ivs, void *ivs_out, const void *in, void *out)
+{
+    return chained_encrypt_batch_host(0, rk, nr, n_msgs, msg_len, ivs, ivs_out, in, out);
+}
+
+int bc_aes_cfb128_encrypt_batch_host(const uint32_t *rk, int nr, size_t n_msgs, size_t msg_len,
+                                     const void *ivs, void *ivs_out, const void *in, void *out)
+{
+    return chained_encrypt_batch_host(1, rk, nr, n_msgs, msg_len, ivs, ivs_out, in, out);
 }
 
 /* ---------------------------------------------------------- RC4 batched */

@@ -102,6 +102,23 @@ def main():
     }
     kat["monte_carlo"] = {"iterations": 10000, "keybits": [128, 192, 256], **mc_expected}
 
+    # SP 800-38A F.3.13-F.3.18 CFB128 vectors as held by the reference (aes.c:958-1015; the mode itself
+    # is compiled out of the reference build, oracle/Makefile turns it on with the source's own switch)
+    cfb_ct = {
+        128: "3b3fd92eb72dad20333449f8e83cfb4ac8a64537a0b3a93fcde3cdad9f1ce58b26751f67a3cbb140b1808cf187a4f4dfc04b05357c5d1c0eeac4c66f9ff7f2e6",
+        192: "cdc80d6fddf18cab34c25909c99a417467ce7f7f81173621961a2b70171d3d7a2e1e8a1dd59b88b1c8e60fed1efac4c9c05f9f9ca9834fa042ae8fba584b09ff",
+        256: "dc7e84bfda79164b7ecd8486985d386039ffed143b28b1c832113c6331e5407bdf10132415e54b92a13ed0a8267ae2f975a385741ab9cef82031623d55b1e471",
+    }
+    k192 = h("8e73b0f7da0e6452c810f32b809079e562f8ead2522c6b7b")
+    cfb = []
+    for kb, key in ((128, k128), (192, k192), (256, k256)):
+        c, off, ivo = ref.aes_cfb128(key, ENC, iv, pt)
+        assert c.tobytes().hex() == cfb_ct[kb] and off == 0
+        p2, off, ivo2 = ref.aes_cfb128(key, DEC, iv, c)
+        assert p2.tobytes() == pt
+        cfb.append({"keybits": kb, "key": key.hex(), "iv": iv.hex(), "pt": pt.hex(), "ct": cfb_ct[kb], "iv_out": ivo.hex()})
+    kat["cfb128"] = cfb
+
     # RC4 (arc4.c:124-143) + the "Key"/"Plaintext" check of SURVEY Appendix B
     rc4 = []
     for key, p, c in (("0123456789abcdef", "0123456789abcdef", "75b7878099e0c596"),
@@ -127,6 +144,10 @@ def main():
     ks, x, y, m = ref.arc4_keystream(b"Secret", [7, 293])
     edge["arc4_chained"] = {"key": b"Secret".hex(), "lengths": [7, 293], "keystream": ks.tobytes().hex(),
                             "x": x, "y": y, "m": m.hex()}
+    data = bytes((i * 11 + 5) & 0xFF for i in range(150))
+    c, off, ivo = ref.aes_cfb128(key, ENC, h("cd" * 16), data)
+    edge["cfb_150"] = {"key": key.hex(), "iv": "cd" * 16, "pt": data.hex(), "ct": c.tobytes().hex(),
+                       "iv_off_out": off, "iv_out": ivo.hex(), "chunks": [3, 40, 0, 16, 91]}
     kat["edge"] = edge
     json.dump(kat, open(os.path.join(HERE, "kat.json"), "w"), indent=1)
 
@@ -144,6 +165,8 @@ def main():
         dg[f"cbc{kb}_enc"] = sha(ref.aes_cbc(key, ENC, z, msg)[1])
         dg[f"cbc{kb}_dec"] = sha(ref.aes_cbc(key, DEC, z, msg)[1])
         dg[f"ctr{kb}"] = sha(ref.aes_ctr(key, z, msg)[0])
+        dg[f"cfb{kb}_enc"] = sha(ref.aes_cfb128(key, ENC, z, msg)[0])
+        dg[f"cfb{kb}_dec"] = sha(ref.aes_cfb128(key, DEC, z, msg)[0])
     keys = msg[: 4096 * 16]
     dg["rc4_4096x4k"] = sha(ref.arc4_batch(keys, 16, msg, 4096))
     # cross-check against SURVEY Appendix C
@@ -189,6 +212,12 @@ def main():
             ent["aesni_ivec"], ent["aesni_nonce"] = "fffffffffffffffe", "01020304"   # 64-bit counter wraps inside
             ent["aesni_ctr"] = ref.aesni_ctr(ref.packed_schedule(key, ENC), 6 + kb // 32,
                                              h(ent["aesni_ivec"]), h(ent["aesni_nonce"]), data).tobytes().hex()
+        rng2 = np.random.default_rng(kb)              # separate stream: keeps the older vectors stable
+        rag = rng2.integers(0, 256, 1000 + kb // 8 + 7, dtype=np.uint8)
+        c, off, ivo = ref.aes_cfb128(key, ENC, ivv, rag)
+        ent["cfb_data"], ent["cfb_enc"], ent["cfb_enc_off"], ent["cfb_enc_iv_out"] = rag.tobytes().hex(), c.tobytes().hex(), off, ivo.hex()
+        c, off, ivo = ref.aes_cfb128(key, DEC, ivv, rag)
+        ent["cfb_dec"], ent["cfb_dec_off"], ent["cfb_dec_iv_out"] = c.tobytes().hex(), off, ivo.hex()
         vec.append(ent)
     k256 = rng.integers(0, 256, 32, dtype=np.uint8).tobytes()
     aes256_sched = ref.aesni_key256(k256)

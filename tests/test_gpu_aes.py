@@ -100,6 +100,57 @@ def test_committed_vectors(pkg, golden):
         assert got.tobytes().hex() == v["aesni_ctr"]                              # 64-bit counter wrap inside
 
 
+def test_cfb128_dropin_and_device(pkg, orc, golden):
+    """aes_crypt_cfb128 (aes.h:124, aes.c:822-862): SP 800-38A vectors of aes.c:958-1015, byte-granular
+    chaining with *iv_off, ragged lengths, in place; then the device entry points vs the oracle."""
+    for v in golden["kat"]["cfb128"]:
+        rc, e = pkg.aes_setkey_enc(h(v["key"]))
+        rc, c, off, ivo = pkg.aes_crypt_cfb128(e, ENC, h(v["iv"]), h(v["pt"]))
+        assert (rc, c.tobytes().hex(), off, ivo.hex()) == (0, v["ct"], 0, v["iv_out"])
+        rc, p, off, ivo = pkg.aes_crypt_cfb128(e, DEC, h(v["iv"]), h(v["ct"]), inplace=True)
+        assert (rc, p.tobytes().hex()) == (0, v["pt"])
+    v = golden["kat"]["edge"]["cfb_150"]
+    rc, e = pkg.aes_setkey_enc(h(v["key"]))
+    for mode, src, dst in ((ENC, "pt", "ct"), (DEC, "ct", "pt")):
+        data, iv, off, outs, pos = h(v[src]), h(v["iv"]), 0, [], 0
+        for n in v["chunks"]:                                        # 3 + 40 + 0 + 16 + 91
+            rc, o, off, iv = pkg.aes_crypt_cfb128(e, mode, iv, data[pos:pos + n], off)
+            assert rc == 0
+            outs.append(o.tobytes())
+            pos += n
+        assert b"".join(outs).hex() == v[dst]
+        assert (off, iv.hex()) == (v["iv_off_out"], v["iv_out"])
+    for v in golden["vectors"]["aes"]:
+        rc, e = pkg.aes_setkey_enc(h(v["key"]))
+        rc, c, off, ivo = pkg.aes_crypt_cfb128(e, ENC, h(v["iv"]), h(v["cfb_data"]))
+        assert (c.tobytes().hex(), off, ivo.hex()) == (v["cfb_enc"], v["cfb_enc_off"], v["cfb_enc_iv_out"])
+        rc, c, off, ivo = pkg.aes_crypt_cfb128(e, DEC, h(v["iv"]), h(v["cfb_data"]))
+        assert (c.tobytes().hex(), off, ivo.hex()) == (v["cfb_dec"], v["cfb_dec_off"], v["cfb_dec_iv_out"])
+    rng = np.random.default_rng(31)
+    for kb, n_msgs, msg_len in ((128, 1, 16 * 1000 + 16), (256, 77, 4096), (192, 600, 48)):
+        key = rng.integers(0, 256, kb // 8, dtype=np.uint8).tobytes()
+        rke, nr = G.sched(pkg, key, ENC)
+        data = rng.integers(0, 256, n_msgs * msg_len, dtype=np.uint8)
+        ivs = rng.integers(0, 256, n_msgs * 16, dtype=np.uint8)
+        want = np.concatenate([orc.aes_cfb128(key, ENC, ivs[16 * m:16 * m + 16].tobytes(),
+                                              data[m * msg_len:(m + 1) * msg_len])[0] for m in range(n_msgs)])
+        d_in, d_out = G.to_dev(data), G.to_dev(np.zeros_like(data))
+        d_iv, d_ivo = G.to_dev(ivs), G.to_dev(np.zeros_like(ivs))
+        pkg.check(pkg.lib().bc_aes_cfb128_encrypt_batch_dev(rke.ctypes.data, nr, n_msgs, msg_len, d_iv.data_ptr(),
+                                                            d_ivo.data_ptr(), d_in.data_ptr(), d_out.data_ptr(), G.stream()))
+        assert np.array_equal(G.host(d_out), want)
+        assert np.array_equal(G.host(d_ivo).reshape(n_msgs, 16), want.reshape(n_msgs, msg_len)[:, -16:])
+        # block-parallel decrypt of the whole buffer as one chain, out of place and in place
+        iv0 = rng.integers(0, 256, 16, dtype=np.uint8).tobytes()
+        wantd = orc.aes_cfb128(key, DEC, iv0, data)[0]
+        pkg.check(pkg.lib().bc_aes_cfb128_decrypt_dev(rke.ctypes.data, nr, iv0, d_in.data_ptr(), d_out.data_ptr(),
+                                                      data.size, G.stream()))
+        assert np.array_equal(G.host(d_out), wantd)
+        pkg.check(pkg.lib().bc_aes_cfb128_decrypt_dev(rke.ctypes.data, nr, iv0, d_in.data_ptr(), d_in.data_ptr(),
+                                                      data.size, G.stream()))
+        assert np.array_equal(G.host(d_in), wantd)
+
+
 # ------------------------------------------------- config 1: 16 MiB digests
 
 def test_golden_digests_16mib_device(pkg, golden, harness_input):
@@ -123,6 +174,8 @@ def test_golden_digests_16mib_device(pkg, golden, harness_input):
         assert sha(G.host(d_out)) == dg[f"cbc{kb}_dec"]
         G.ctr_dev(pkg, rke, nr, z, d_in, d_out, n)
         assert sha(G.host(d_out)) == dg[f"ctr{kb}"]
+        pkg.check(pkg.lib().bc_aes_cfb128_decrypt_dev(rke.ctypes.data, nr, z, d_in.data_ptr(), d_out.data_ptr(), n, G.stream()))
+        assert sha(G.host(d_out)) == dg[f"cfb{kb}_dec"]
         # AES_CTR_encrypt(ivec="HloEelAS", nonce="315A") as aes-modes/test.c:305-308
         assert sha(pkg.AES_CTR_encrypt(msg, b"HloEelAS", b"315A", pkg.AES_Key_Expansion(key), nr)) == dg[f"aesni_ctr{kb}"]
         # CBC encrypt of the whole 16 MiB as ONE message (serial chain, one GPU thread): 128-bit only, it is slow

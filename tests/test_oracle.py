@@ -51,6 +51,29 @@ def test_rfc3686_ctr(impl, golden):
         assert back.tobytes().hex() == v["pt"]
 
 
+def test_cfb128(impl, golden):
+    """SP 800-38A CFB128 vectors of aes.c:958-1015 and the byte-granular chaining of aes.c:822-862."""
+    for v in golden["kat"]["cfb128"]:
+        c, off, ivo = impl.aes_cfb128(h(v["key"]), ENC, h(v["iv"]), h(v["pt"]))
+        assert (c.tobytes().hex(), off, ivo.hex()) == (v["ct"], 0, v["iv_out"])
+        p, off, ivo = impl.aes_cfb128(h(v["key"]), DEC, h(v["iv"]), h(v["ct"]))
+        assert p.tobytes().hex() == v["pt"]
+    v = golden["kat"]["edge"]["cfb_150"]
+    for mode, src, dst in ((ENC, "pt", "ct"), (DEC, "ct", "pt")):
+        data, iv, off, outs, pos = h(v[src]), h(v["iv"]), 0, [], 0
+        for n in v["chunks"]:
+            o, off, iv = impl.aes_cfb128(h(v["key"]), mode, iv, data[pos:pos + n], off)
+            outs.append(o.tobytes())
+            pos += n
+        assert b"".join(outs).hex() == v[dst]
+        assert (off, iv.hex()) == (v["iv_off_out"], v["iv_out"])
+    for v in golden["vectors"]["aes"]:
+        c, off, ivo = impl.aes_cfb128(h(v["key"]), ENC, h(v["iv"]), h(v["cfb_data"]))
+        assert (c.tobytes().hex(), off, ivo.hex()) == (v["cfb_enc"], v["cfb_enc_off"], v["cfb_enc_iv_out"])
+        c, off, ivo = impl.aes_cfb128(h(v["key"]), DEC, h(v["iv"]), h(v["cfb_data"]))
+        assert (c.tobytes().hex(), off, ivo.hex()) == (v["cfb_dec"], v["cfb_dec_off"], v["cfb_dec_iv_out"])
+
+
 def test_monte_carlo(orc, golden):
     """aes_self_test's ECB/CBC loops (aes.c:1106-1212): zero key, 10 000 chained blocks."""
     mc = golden["kat"]["monte_carlo"]
@@ -165,6 +188,8 @@ def test_golden_digests_16mib(orc, golden, harness_input):
         assert sha(orc.aes_cbc(key, ENC, z, msg)[1]) == dg[f"cbc{kb}_enc"]
         assert sha(orc.aes_cbc(key, DEC, z, msg)[1]) == dg[f"cbc{kb}_dec"]
         assert sha(orc.aes_ctr(key, z, msg)[0]) == dg[f"ctr{kb}"]
+        assert sha(orc.aes_cfb128(key, ENC, z, msg)[0]) == dg[f"cfb{kb}_enc"]
+        assert sha(orc.aes_cfb128(key, DEC, z, msg)[0]) == dg[f"cfb{kb}_dec"]
         assert sha(orc.aesni_ctr(orc.packed_schedule(key), 6 + kb // 32, b"HloEelAS", b"315A", msg)) == dg[f"aesni_ctr{kb}"]
     assert sha(orc.arc4_batch(msg[: 4096 * 16], 16, msg, 4096)) == dg["rc4_4096x4k"]
     o, ivo = orc.aes_cbc_encrypt_batch(key32, msg[: 256 * 16].copy(), msg, 65536)
