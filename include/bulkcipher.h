@@ -79,6 +79,12 @@ int bc_aes_ctr_dev(const uint32_t *rk, int nr, const unsigned char counter[16], 
 int bc_aes_ecb_dev(const uint32_t *rk, int nr, int mode, const void *d_in, void *d_out,
                    size_t nbytes, void *stream);
 
+/* ECB where each block is four BIG-endian 32-bit words in memory: the uint[] block
+ * interface of the reference's C++ class AES (aes-gpu/Source/AES.h:84-147, GETWORD /
+ * PUTWORD at AES.cu:42-43, byte2int/int2byte at AES.cu:190-203).  include/AES.h wraps it. */
+int bc_aes_ecb_be32_dev(const uint32_t *rk, int nr, int mode, const void *d_in, void *d_out,
+                        size_t nbytes, void *stream);
+
 /* CBC decrypt, parallel over blocks.  Replaces aes_crypt_cbc(AES_DECRYPT)
  * (aes-modes/aes.c:784-797).  iv (host, 16 bytes) is read only; the caller gets
  * the new iv as the last ciphertext block (aes.c:792).  in == out is allowed
@@ -160,6 +166,7 @@ int bc_aes_ctr_host(const uint32_t *rk, int nr, const unsigned char counter[16],
                     uint64_t first_block, const void *in, void *out, size_t nbytes,
                     unsigned char last_keystream[16]);
 int bc_aes_ecb_host(const uint32_t *rk, int nr, int mode, const void *in, void *out, size_t nbytes);
+int bc_aes_ecb_be32_host(const uint32_t *rk, int nr, int mode, const void *in, void *out, size_t nbytes);
 int bc_aes_cbc_decrypt_host(const uint32_t *rk, int nr, const unsigned char iv[16],
                             const void *in, void *out, size_t nbytes);
 int bc_aes_cbc_encrypt_batch_host(const uint32_t *rk, int nr, size_t n_msgs, size_t msg_len,
@@ -181,6 +188,12 @@ int bc_xor_host(const void *a, const void *b, void *out, size_t nbytes);
  * Equivalent to one bc_aes_ctr_host call. */
 int bc_aes_ctr_host_multi(int n_gpus, const uint32_t *rk, int nr, const unsigned char counter[16],
                           int counter_bits, const void *in, void *out, size_t nbytes);
+
+/* ---- key schedules as plain word arrays (what aes_setkey_enc/dec compute) ---- */
+/* FIPS-197 expansion on little-endian words (aes-modes/aes.c:469-539); returns nr (10/12/14) or 0. */
+int  bc_aes_expand_key(const unsigned char *key, unsigned int keybits, uint32_t rk[60]);
+/* Equivalent-inverse-cipher schedule from an encryption schedule (aes-modes/aes.c:563-594). */
+void bc_aes_invert_key(const uint32_t enc[60], int nr, uint32_t dec[60]);
 
 #ifdef __cplusplus
 }

@@ -45,7 +45,8 @@ BC_SYMBOLS = [
     "bc_aes_ctr_dev", "bc_aes_ecb_dev", "bc_aes_cbc_decrypt_dev", "bc_aes_cbc_encrypt_batch_dev",
     "bc_arc4_batch_dev", "bc_xor_dev", "bc_aes_cbc_decrypt_inplace_noalloc_dev",
     "bc_aes_cfb128_decrypt_dev", "bc_aes_cfb128_encrypt_batch_dev", "bc_aes_cfb128_decrypt_host",
-    "bc_aes_cfb128_encrypt_batch_host",
+    "bc_aes_cfb128_encrypt_batch_host", "bc_aes_ecb_be32_dev", "bc_aes_ecb_be32_host",
+    "bc_aes_expand_key", "bc_aes_invert_key",
     "bc_aes_ctr_host", "bc_aes_ecb_host", "bc_aes_cbc_decrypt_host", "bc_aes_cbc_encrypt_batch_host",
     "bc_arc4_batch_host", "bc_xor_host", "bc_aes_ctr_host_multi",
 ]

@@ -405,6 +405,7 @@ struct BlkArgs {
     uint64_t n_groups;       /* ceil(nblocks / 256) */
     uint4 iv;                /* CBC: block before block 0 */
     const uint4 *boundary;   /* CBC in-place: boundary[g] = ciphertext block 256*g - 1 (g >= 1) */
+    uint32_t be32;           /* 1: blocks are four BIG-endian 32-bit words in memory (aes-gpu's uint[] interface) */
 };
 
 template <int NR, int MODE>
@@ -438,6 +439,10 @@ aes_blocks_kernel(const __grid_constant__ AesSched ks, const __grid_constant__ B
             const bool live = full || b < a.nblocks;
             uint4 c = make_uint4(0, 0, 0, 0);
             if (live) c = ld_stream(a.in + b);
+            if (!CHAIN && a.be32) {                /* GETWORD/PUTWORD of aes-gpu/Source/AES.cu:42-43: swap to the byte stream */
+                c.x = __byte_perm(c.x, 0, 0x0123); c.y = __byte_perm(c.y, 0, 0x0123);
+                c.z = __byte_perm(c.z, 0, 0x0123); c.w = __byte_perm(c.w, 0, 0x0123);
+            }
             uint4 prev = make_uint4(0, 0, 0, 0);
             if (CHAIN) {                           /* C_{i-1}: the lane to the left, lane 0 from the previous row */
                 prev.x = __shfl_up_sync(0xffffffffu, c.x, 1);
@@ -458,6 +463,10 @@ aes_blocks_kernel(const __grid_constant__ AesSched ks, const __grid_constant__ B
                 s.a ^= prev.x; s.b ^= prev.y; s.c ^= prev.z; s.d ^= prev.w;
             } else if (MODE == MODE_CFB_DEC) {
                 s.a ^= c.x; s.b ^= c.y; s.c ^= c.z; s.d ^= c.w;
+            }
+            if (!CHAIN && a.be32) {
+                s.a = __byte_perm(s.a, 0, 0x0123); s.b = __byte_perm(s.b, 0, 0x0123);
+                s.c = __byte_perm(s.c, 0, 0x0123); s.d = __byte_perm(s.d, 0, 0x0123);
             }
             if (live) st_stream(a.out + b, make_uint4(s.a, s.b, s.c, s.d));
         }
@@ -770,8 +779,9 @@ extern "C" int bc_aes_ctr_dev(const uint32_t *rk, int nr, const unsigned char co
     }
 }
 
-extern "C" int bc_aes_ecb_dev(const uint32_t *rk, int nr, int mode, const void *d_in, void *d_out,
-                              size_t nbytes, void *stream)
+namespace {
+
+int ecb_dev(const uint32_t *rk, int nr, int mode, const void *d_in, void *d_out, size_t nbytes, void *stream, uint32_t be32)
 {
     int rc = check_common(rk, nr, d_in, d_out, nbytes);
     if (rc) return rc;
@@ -787,10 +797,25 @@ extern "C" int bc_aes_ecb_dev(const uint32_t *rk, int nr, int mode, const void *
     a.out = (uint4 *)d_out;
     a.nblocks = nbytes / 16;            /* whole blocks only, like the harness loop */
     a.n_groups = (a.nblocks + 255) / 256;
+    a.be32 = be32;
     if (a.nblocks == 0) return BC_OK;
     cudaStream_t st = (cudaStream_t)stream;
     return mode == BC_ENCRYPT ? launch_blocks_nr<MODE_ECB_ENC>(nr, ks, a, st)
                               : launch_blocks_nr<MODE_ECB_DEC>(nr, ks, a, st);
+}
+
+}  // namespace
+
+extern "C" int bc_aes_ecb_dev(const uint32_t *rk, int nr, int mode, const void *d_in, void *d_out,
+                              size_t nbytes, void *stream)
+{
+    return ecb_dev(rk, nr, mode, d_in, d_out, nbytes, stream, 0u);
+}
+
+extern "C" int bc_aes_ecb_be32_dev(const uint32_t *rk, int nr, int mode, const void *d_in, void *d_out,
+                                   size_t nbytes, void *stream)
+{
+    return ecb_dev(rk, nr, mode, d_in, d_out, nbytes, stream, 1u);
 }
 
 namespace {

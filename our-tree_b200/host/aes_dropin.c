@@ -41,7 +41,7 @@ static uint32_t inv_mix_column(uint32_t w)
     return (uint32_t)o[0] | ((uint32_t)o[1] << 8) | ((uint32_t)o[2] << 16) | ((uint32_t)o[3] << 24);
 }
 
-/* FIPS-197 expansion on little-endian words (aes.c:469-539); returns nr or 0. */
+/* FIPS-197 expansion on little-endian words (aes.c:469-539); returns nr or 0.  Declared in bulkcipher.h. */
 int bc_aes_expand_key(const unsigned char *key, unsigned int keybits, uint32_t rk[60])
 {
     if (keybits != 128 && keybits != 192 && keybits != 256) return 0;

@@ -389,16 +389,16 @@ int bc_aes_ctr_host(const uint32_t *rk, int nr, const unsigned char counter[16],
 
 /* ------------------------------------------------------------- AES-ECB */
 
-typedef struct { const uint32_t *rk; int nr; int mode; } ecb_op;
+typedef struct { const uint32_t *rk; int nr; int mode; int be32; } ecb_op;
 
 static int ecb_chunk(void *arg, size_t idx, size_t off, size_t n, void *d, cudaStream_t st)
 {
     ecb_op *o = (ecb_op *)arg;
     (void)idx; (void)off;
-    return bc_aes_ecb_dev(o->rk, o->nr, o->mode, d, d, n, st);
+    return (o->be32 ? bc_aes_ecb_be32_dev : bc_aes_ecb_dev)(o->rk, o->nr, o->mode, d, d, n, st);
 }
 
-int bc_aes_ecb_host(const uint32_t *rk, int nr, int mode, const void *in, void *out, size_t nbytes)
+static int ecb_host(int be32, const uint32_t *rk, int nr, int mode, const void *in, void *out, size_t nbytes)
 {
     int rc = check_host_args(rk, nr, in, out, nbytes);
     if (rc) return rc;
@@ -407,16 +407,26 @@ int bc_aes_ecb_host(const uint32_t *rk, int nr, int mode, const void *in, void *
     bc_dev *d;
     if ((rc = dev_prepare(&d))) return rc;
     if (classify(in) == 2 && classify(out) == 2) {
-        rc = bc_aes_ecb_dev(rk, nr, mode, in, out, nbytes, NULL);
+        rc = (be32 ? bc_aes_ecb_be32_dev : bc_aes_ecb_dev)(rk, nr, mode, in, out, nbytes, NULL);
         return rc ? rc : bc_device_sync();
     }
     pthread_mutex_lock(&d->lock);
     if ((rc = dev_ensure_slots(d)) == BC_OK) {
-        ecb_op o = { rk, nr, mode };
+        ecb_op o = { rk, nr, mode, be32 };
         rc = run_pipeline(d, (const unsigned char *)in, (unsigned char *)out, nbytes, BC_CHUNK_BYTES, ecb_chunk, &o);
     }
     pthread_mutex_unlock(&d->lock);
     return rc;
+}
+
+int bc_aes_ecb_host(const uint32_t *rk, int nr, int mode, const void *in, void *out, size_t nbytes)
+{
+    return ecb_host(0, rk, nr, mode, in, out, nbytes);
+}
+
+int bc_aes_ecb_be32_host(const uint32_t *rk, int nr, int mode, const void *in, void *out, size_t nbytes)
+{
+    return ecb_host(1, rk, nr, mode, in, out, nbytes);
 }
 
 /* ------------------------------------------------------ AES-CBC decrypt */

@@ -35,3 +35,10 @@ def test_rc4_harness():
     out = run([os.path.join(BUILD, "rc4_test"), "--iters", "3", "--single-bytes", "65536"])
     assert "all outputs verified" in out and "MISMATCH" not in out
     assert "Generated a new key in" in out          # the reference's line (test.c:84)
+
+
+def test_aes_gpu_cpp_facade():
+    """include/AES.h: the reference's `class AES : BlockCipher` (aes-gpu/Source/AES.h:84-147) over the engine."""
+    out = run([os.path.join(BUILD, "aes_gpu_facade_test")])
+    assert "all outputs verified" in out and "MISMATCH" not in out
+    assert out.count("FIPS-197") == 3 and "Invalid AES key size" in out
