@@ -278,12 +278,15 @@ def run_ours(args):
     rc, ctx = pkg.aes_setkey_enc(KEY)
     rk = pkg.schedule_words(ctx)
     nr = ctx.nr
-    nbytes = SHARD_BYTES
+    nbytes = int(args.shard_gib * GIB) // 65536 * 65536
     blocks = nbytes // 16
     first_block = rank * blocks                                   # shard by counter offset
 
-    d_in = torch.randint(0, 256, (nbytes,), dtype=torch.uint8, device="cuda")   # synthetic random plaintext
-    d_out = torch.empty_like(d_in)
+    d_in = torch.empty(nbytes, dtype=torch.uint8, device="cuda")                 # synthetic random plaintext
+    for off in range(0, nbytes, 4 * GIB):
+        d_in[off:off + 4 * GIB].random_(0, 256)
+    in_place = nbytes > 48 * GIB                                                 # config 5 at 2 GPUs: 128 GiB per GPU
+    d_out = d_in if in_place else torch.empty_like(d_in)
     st = torch.cuda.current_stream().cuda_stream
 
     def step():
@@ -334,8 +337,8 @@ def run_ours(args):
     # The 4 GiB shard streams through a pinned window; at N <= 2 the window is the whole shard,
     # at N > 2 it is 1 GiB walked four times with the counter offset advancing (same bytes over
     # the link per step, 2 GiB instead of 8 GiB of pinned host memory per rank).
-    e2e_bytes = nbytes
-    window = nbytes if n_gpus <= 2 else GIB
+    e2e_bytes = min(nbytes, SHARD_BYTES)
+    window = e2e_bytes if n_gpus <= 2 else GIB
     h_in = h_out = None
     while window >= (64 << 20):
         h_in, h_out = L.bc_host_alloc(window), L.bc_host_alloc(window)
@@ -387,7 +390,9 @@ def run_ours(args):
         return 0
 
     # ---- the rest of BASELINE.json's metric / configs, device resident, on this rank's GPU
-    others = other_workloads(pkg, L, d_in, d_out, st, measured_peak()[0]) if not args.no_others else None
+    others = None
+    if not args.no_others and not in_place and nbytes == SHARD_BYTES:
+        others = other_workloads(pkg, L, d_in, d_out, st, measured_peak()[0])
 
     peak, peak_src = measured_peak()
     value = n_gpus * nbytes * args.steps / (total_ms * 1e-3) / 1e9
@@ -400,10 +405,11 @@ def run_ours(args):
         "metric": METRIC, "value": round(value, 2), "unit": UNIT, "n_gpus": n_gpus, "steps": args.steps,
         "warmup": args.warmup, "ms_per_step": round(total_ms / args.steps, 4), "higher_is_better": True,
         "scaling": "weak", "vs_baseline": None, "dtype": "u32", "data": "synthetic",
-        "config": {"workload": "AES-128-CTR encrypt of a 4 GiB synthetic buffer per GPU (BASELINE configs[1]); "
+        "config": {"workload": f"AES-128-CTR encrypt of a {nbytes / GIB:g} GiB synthetic buffer per GPU "
+                               "(BASELINE configs[1] at 4 GiB; configs[4] with --shard-gib 256/N); "
                                "N GPUs shard by counter offset, no collective",
                    "key_bits": 128, "bytes_per_gpu": nbytes, "counter": COUNTER.hex(),
-                   "l2": "inputs (4 GiB) larger than L2 (126 MB); no flush needed", "in_place": False},
+                   "l2": "inputs (>= 4 GiB) larger than L2 (126 MB); no flush needed", "in_place": in_place},
         "roofline": {"bound": "hbm", "achieved": round(achieved, 1), "peak": peak, "unit": "GB/s",
                      "frac": round(achieved / peak, 4), "traffic": profile_traffic(),
                      "kernel": "aes_ctr_kernel<10,1024>", "kernel_ms": round(kernel_ms, 4), "peak_source": peak_src,
@@ -440,6 +446,8 @@ def main():
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-others", action="store_true", help="skip the configs 3/4 side measurements")
+    ap.add_argument("--shard-gib", type=float, default=4.0,
+                    help="bytes per GPU in GiB (default 4 = BASELINE configs[1]; 256/N reproduces config 5)")
     args = ap.parse_args()
     args.warmup = max(args.warmup, 3) if args.impl == "ours" else args.warmup
     if args.impl == "reference":
@@ -449,7 +457,8 @@ def main():
         # convenience: re-launch ourselves under torchrun, one rank per GPU
         cmd = [sys.executable, "-m", "torch.distributed.run", "--nnodes=1", f"--nproc-per-node={args.gpus}",
                "--master-addr", "127.0.0.1", "--master-port", os.environ.get("MASTER_PORT", "29511"), __file__,
-               "--gpus", str(args.gpus), "--steps", str(args.steps), "--warmup", str(args.warmup)]
+               "--gpus", str(args.gpus), "--steps", str(args.steps), "--warmup", str(args.warmup),
+               "--shard-gib", str(args.shard_gib)] + (["--no-others"] if args.no_others else [])
         return subprocess.call(cmd)
     return run_ours(args)
 

@@ -248,6 +248,33 @@ def test_ctr_random_sizes_and_carries(pkg, orc, kb):
                 assert np.array_equal(G.host(d_out2)[:n], want)
 
 
+def test_ctr_config5_shard_offsets(pkg, orc):
+    """BASELINE config 5: 256 GiB = 2^34 blocks sharded over 2/4/8 GPUs by counter offset.  The buffer
+    itself does not fit a test, but every shard start does: windows at first_block = g * 2^34 / G,
+    straddling the 2^32 block seams (64 GiB * k) and the end of the 256 GiB stream, vs the oracle
+    run on counter + first_block."""
+    rng = np.random.default_rng(55)
+    key = rng.integers(0, 256, 16, dtype=np.uint8).tobytes()
+    rke, nr = G.sched(pkg, key, 1)
+    nc = bytes.fromhex("0f1e2d3c4b5a69788796a5b4fffffff0")
+    total = 1 << 34
+    starts = sorted({g * total // n for n in (2, 4, 8) for g in range(n)} |
+                    {k * (1 << 32) - 700 for k in (1, 2, 3)} | {total - 1000, (1 << 32) - 16 - 0xfffffff0 % 256})
+    data = rng.integers(0, 256, 16 * 1500, dtype=np.uint8)
+    d_in, d_out = G.to_dev(data), G.to_dev(np.zeros_like(data))
+    for b0 in starts:
+        G.ctr_dev(pkg, rke, nr, nc, d_in, d_out, data.size, first_block=b0)
+        shifted = ((int.from_bytes(nc, "big") + b0) % (1 << 128)).to_bytes(16, "big")
+        assert np.array_equal(G.host(d_out), orc.aes_ctr(key, shifted, data)[0]), b0
+    # the same offsets under the 64-bit AES-NI rule: only bytes 8..15 move
+    b0 = (1 << 34) - 5
+    G.ctr_dev(pkg, rke, nr, nc, d_in, d_out, data.size, bits=64, first_block=b0)
+    lo = (int.from_bytes(nc[8:], "big") + b0) % (1 << 64)
+    want = np.concatenate([data[16 * i:16 * i + 16] ^ orc.aes_ecb(key, 1, nc[:8] + ((lo + i) % (1 << 64)).to_bytes(8, "big"))
+                           for i in range(40)])
+    assert np.array_equal(G.host(d_out)[:640], want)
+
+
 def test_ctr_64bit_counter_mode(pkg, orc):
     """AES_CTR_encrypt's add never carries out of bytes 8..15 (aesni.c:139,143)."""
     rng = np.random.default_rng(5)
