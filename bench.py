@@ -419,7 +419,7 @@ def run_ours(args):
                                      "gbs": round(lds_bound, 1), "frac": round(value / n_gpus / lds_bound, 4),
                                      "sm_ghz": sm_clock_ghz, "sms": sms}},
         "e2e": {"value": round(e2e_value, 2), "unit": UNIT, "h2d_bytes_per_step": e2e_bytes, "d2h_bytes_per_step": e2e_bytes + 16,
-                "steps": e2e_steps, "api": "bc_aes_ctr_host (pinned host buffers, 32 MiB chunks, 3 streams)",
+                "steps": e2e_steps, "api": "bc_aes_ctr_host (pinned host buffers, 64 MiB chunks, 3 slots, one stream per stage)",
                 "host_window_bytes": window, "calls_per_step": passes},
         "gpu_launches": args.steps, "clocks": clocks,
     }

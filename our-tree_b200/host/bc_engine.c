@@ -26,9 +26,9 @@
 #define BC_MAX_DEVICES 16
 #define BC_MAX_SLOTS   8
 /* Pipeline shape: `g_slots` chunks in flight, each `g_chunk` bytes (a multiple of 4 KiB).
- * Defaults were picked on a B200 / PCIe Gen5 box (tools/pcie_probe.py);
+ * Defaults (64 MiB x 3) were picked on a B200 / PCIe Gen5 box (tools/e2e_probe.py);
  * BULKCIPHER_CHUNK_MIB and BULKCIPHER_SLOTS override them before the first call. */
-static size_t g_chunk = (size_t)32 << 20;
+static size_t g_chunk = (size_t)64 << 20;
 static int    g_slots = 3;
 #define BC_SLOTS       g_slots
 #define BC_CHUNK_BYTES g_chunk
@@ -84,6 +84,9 @@ typedef struct {
     bc_scratch scratch[BC_MAX_SCRATCH];
     unsigned char *d_aux;       /* small device buffer: ivs, keys, contexts, last keystream */
     size_t     aux_cap;
+    /* enqueue-ahead pipeline for pinned callers: one stream per stage, events chain the slots */
+    cudaStream_t s_h2d, s_k, s_d2h;
+    cudaEvent_t  e_h2d[BC_MAX_SLOTS], e_k[BC_MAX_SLOTS], e_d2h[BC_MAX_SLOTS];
 } bc_dev;
 
 static bc_dev g_dev[BC_MAX_DEVICES];
@@ -247,7 +250,13 @@ static int dev_ensure_slots(bc_dev *d)
         BC_CUDA(cudaStreamCreateWithFlags(&s->stream, cudaStreamNonBlocking), "cudaStreamCreate");
         BC_CUDA(cudaEventCreateWithFlags(&s->done, cudaEventDisableTiming), "cudaEventCreate");
         BC_CUDA(cudaMalloc((void **)&s->d_buf, BC_CHUNK_BYTES), "cudaMalloc(pipeline buffer)");
+        BC_CUDA(cudaEventCreateWithFlags(&d->e_h2d[i], cudaEventDisableTiming), "cudaEventCreate");
+        BC_CUDA(cudaEventCreateWithFlags(&d->e_k[i], cudaEventDisableTiming), "cudaEventCreate");
+        BC_CUDA(cudaEventCreateWithFlags(&d->e_d2h[i], cudaEventDisableTiming), "cudaEventCreate");
     }
+    BC_CUDA(cudaStreamCreateWithFlags(&d->s_h2d, cudaStreamNonBlocking), "cudaStreamCreate");
+    BC_CUDA(cudaStreamCreateWithFlags(&d->s_k, cudaStreamNonBlocking), "cudaStreamCreate");
+    BC_CUDA(cudaStreamCreateWithFlags(&d->s_d2h, cudaStreamNonBlocking), "cudaStreamCreate");
     d->ready = 1;
     return BC_OK;
 }
@@ -296,10 +305,46 @@ typedef int (*chunk_fn)(void *arg, size_t chunk_idx, size_t off, size_t n, void 
 
 /* Run `fn` over [in, in+nbytes) in chunks of `chunk` bytes (<= BC_CHUNK_BYTES),
  * each chunk H2D -> fn (in place on the device) -> D2H on its own stream. */
+/* Pinned (or absent) input and pinned output: nothing needs the host between chunks, so the
+ * whole transfer is enqueued up front on three stage streams — all H2D copies back to back on
+ * one, kernels on the second, D2H copies on the third — with events handing each slot from
+ * stage to stage and back.  Both copy engines then run without waiting for the host. */
+static int run_pipeline_enqueued(bc_dev *d, const unsigned char *in, unsigned char *out, size_t nbytes,
+                                 size_t chunk, chunk_fn fn, void *arg)
+{
+    int rc = BC_OK;
+    size_t idx = 0;
+    for (size_t off = 0; off < nbytes && rc == BC_OK; off += chunk, idx++) {
+        const size_t n = nbytes - off < chunk ? nbytes - off : chunk;
+        const int sl = (int)(idx % BC_SLOTS);
+        bc_slot *s = &d->slot[sl];
+        if (in) {
+            if (idx >= (size_t)BC_SLOTS) BC_CUDA(cudaStreamWaitEvent(d->s_h2d, d->e_d2h[sl], 0), "cudaStreamWaitEvent");
+            BC_CUDA(cudaMemcpyAsync(s->d_buf, in + off, n, cudaMemcpyHostToDevice, d->s_h2d), "cudaMemcpyAsync H2D");
+            BC_CUDA(cudaEventRecord(d->e_h2d[sl], d->s_h2d), "cudaEventRecord");
+            BC_CUDA(cudaStreamWaitEvent(d->s_k, d->e_h2d[sl], 0), "cudaStreamWaitEvent");
+        } else if (idx >= (size_t)BC_SLOTS) {
+            BC_CUDA(cudaStreamWaitEvent(d->s_k, d->e_d2h[sl], 0), "cudaStreamWaitEvent");
+        }
+        if ((rc = fn(arg, idx, off, n, s->d_buf, d->s_k))) break;
+        BC_CUDA(cudaEventRecord(d->e_k[sl], d->s_k), "cudaEventRecord");
+        BC_CUDA(cudaStreamWaitEvent(d->s_d2h, d->e_k[sl], 0), "cudaStreamWaitEvent");
+        BC_CUDA(cudaMemcpyAsync(out + off, s->d_buf, n, cudaMemcpyDeviceToHost, d->s_d2h), "cudaMemcpyAsync D2H");
+        BC_CUDA(cudaEventRecord(d->e_d2h[sl], d->s_d2h), "cudaEventRecord");
+    }
+    cudaError_t e1 = cudaStreamSynchronize(d->s_d2h), e2 = cudaStreamSynchronize(d->s_k), e3 = cudaStreamSynchronize(d->s_h2d);
+    if (rc == BC_OK && e1 != cudaSuccess) rc = bc_cuda_fail((int)e1, "cudaStreamSynchronize(D2H)");
+    if (rc == BC_OK && e2 != cudaSuccess) rc = bc_cuda_fail((int)e2, "cudaStreamSynchronize(kernels)");
+    if (rc == BC_OK && e3 != cudaSuccess) rc = bc_cuda_fail((int)e3, "cudaStreamSynchronize(H2D)");
+    return rc;
+}
+
 static int run_pipeline(bc_dev *d, const unsigned char *in, unsigned char *out, size_t nbytes,
                         size_t chunk, chunk_fn fn, void *arg)
 {
     const int in_pinned = in && classify(in) == 1, out_pinned = classify(out) == 1;
+    if ((in_pinned || !in) && out_pinned && !getenv("BULKCIPHER_HOST_IN_LOOP"))
+        return run_pipeline_enqueued(d, in, out, nbytes, chunk, fn, arg);
     int rc = BC_OK;
     size_t idx = 0;
     for (size_t off = 0; off < nbytes && rc == BC_OK; off += chunk, idx++) {
@@ -331,6 +376,16 @@ static int run_pipeline(bc_dev *d, const unsigned char *in, unsigned char *out, 
     }
     if (rc != BC_OK) { for (int k = 0; k < BC_SLOTS; k++) { cudaStreamSynchronize(d->slot[k].stream); d->slot[k].pend_dst = NULL; } }
     return rc;
+}
+
+/* Chunk size for a transfer of nbytes: the full granule for big buffers, about an eighth of
+ * the buffer (whole MiB, at least 4 MiB) for smaller ones so that copies still overlap. */
+static size_t pick_chunk(size_t nbytes)
+{
+    if (nbytes >= 8 * BC_CHUNK_BYTES) return BC_CHUNK_BYTES;
+    size_t c = ((nbytes / 8) + ((size_t)1 << 20) - 1) & ~(((size_t)1 << 20) - 1);
+    if (c < ((size_t)4 << 20)) c = (size_t)4 << 20;
+    return c < BC_CHUNK_BYTES ? c : BC_CHUNK_BYTES;
 }
 
 static int check_host_args(const uint32_t *rk, int nr, const void *in, const void *out, size_t nbytes)
@@ -380,7 +435,7 @@ int bc_aes_ctr_host(const uint32_t *rk, int nr, const unsigned char counter[16],
     pthread_mutex_lock(&d->lock);
     if ((rc = dev_ensure_slots(d)) == BC_OK && (rc = dev_ensure_aux(d, 16)) == BC_OK) {
         ctr_op o = { rk, nr, counter, counter_bits, first_block, nbytes, last_keystream ? d->d_aux : NULL };
-        rc = run_pipeline(d, (const unsigned char *)in, (unsigned char *)out, nbytes, BC_CHUNK_BYTES, ctr_chunk, &o);
+        rc = run_pipeline(d, (const unsigned char *)in, (unsigned char *)out, nbytes, pick_chunk(nbytes), ctr_chunk, &o);
         if (rc == BC_OK && last_keystream) rc = bc_memcpy_d2h(last_keystream, d->d_aux, 16);
     }
     pthread_mutex_unlock(&d->lock);
@@ -413,7 +468,7 @@ static int ecb_host(int be32, const uint32_t *rk, int nr, int mode, const void *
     pthread_mutex_lock(&d->lock);
     if ((rc = dev_ensure_slots(d)) == BC_OK) {
         ecb_op o = { rk, nr, mode, be32 };
-        rc = run_pipeline(d, (const unsigned char *)in, (unsigned char *)out, nbytes, BC_CHUNK_BYTES, ecb_chunk, &o);
+        rc = run_pipeline(d, (const unsigned char *)in, (unsigned char *)out, nbytes, pick_chunk(nbytes), ecb_chunk, &o);
     }
     pthread_mutex_unlock(&d->lock);
     return rc;
@@ -456,15 +511,16 @@ static int chained_decrypt_host(int cfb, const uint32_t *rk, int nr, const unsig
     }
     /* Chunk k chains from the last ciphertext block of chunk k-1.  Collect those
      * blocks first: with in == out the pipeline's D2H would overwrite them. */
-    const size_t n_chunks = (nbytes + BC_CHUNK_BYTES - 1) / BC_CHUNK_BYTES;
+    const size_t chunk = pick_chunk(nbytes);
+    const size_t n_chunks = (nbytes + chunk - 1) / chunk;
     unsigned char *ivs = (unsigned char *)malloc(16 * n_chunks);
     if (!ivs) { bc_set_error("out of host memory"); return BC_ERR_BAD_ARG; }
     memcpy(ivs, iv, 16);
-    for (size_t k = 1; k < n_chunks; k++) memcpy(ivs + 16 * k, (const unsigned char *)in + k * BC_CHUNK_BYTES - 16, 16);
+    for (size_t k = 1; k < n_chunks; k++) memcpy(ivs + 16 * k, (const unsigned char *)in + k * chunk - 16, 16);
     pthread_mutex_lock(&d->lock);
     if ((rc = dev_ensure_slots(d)) == BC_OK) {
         cbcd_op o = { rk, nr, ivs, cfb };
-        rc = run_pipeline(d, (const unsigned char *)in, (unsigned char *)out, nbytes, BC_CHUNK_BYTES, cbcd_chunk, &o);
+        rc = run_pipeline(d, (const unsigned char *)in, (unsigned char *)out, nbytes, chunk, cbcd_chunk, &o);
     }
     pthread_mutex_unlock(&d->lock);
     free(ivs);
