@@ -273,6 +273,10 @@ def run_ours(args):
     n_gpus = world if distributed else 1
 
     pkg = g.load_package()
+    if not os.path.exists(pkg.LIB_PATH) and rank == 0:
+        g.build()                                                 # fresh checkout: compile once (nvcc is in the image)
+    if distributed:
+        dist.barrier()
     L = pkg.lib()
     pkg.check(L.bc_set_device(local))
     rc, ctx = pkg.aes_setkey_enc(KEY)

@@ -29,6 +29,22 @@ def load_package():
     return mod
 
 
+@pytest.fixture(scope="session", autouse=True)
+def _built_artifacts():
+    """The in-tree builds normally travel with the snapshot; on a checkout without them
+    (fresh clone) compile once — nvcc cross-compiles without a GPU.  A failed build is not
+    hidden: the tests that need the library then fail loudly in `lib()`."""
+    lib = os.path.join(ROOT, "our-tree_b200", "libbulkcipher.so")
+    harness = os.path.join(ROOT, "our-tree_b200", "build", "aes_test")
+    if not (os.path.exists(lib) and os.path.exists(harness)):
+        try:
+            import __graft_entry__ as g
+            g.build()
+        except Exception as e:  # noqa: BLE001
+            print(f"[conftest] build() failed: {e}")
+    yield
+
+
 @pytest.fixture(scope="session")
 def orc():
     import oracle
