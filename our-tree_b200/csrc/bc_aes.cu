@@ -526,7 +526,14 @@ aes_cbc_enc_batch_kernel(const __grid_constant__ AesSched ks, const __grid_const
  * boxes of 32 messages x 64 bytes (4 blocks of each chain) with one bulk-tensor load
  * and one store, double buffered, so the global side is coalesced although every
  * lane walks its own message.  The chain value never leaves registers. */
-constexpr int kCbcTmaMaxWarps = 24;          /* 128 KB tables + 24 x 4 KB staging fits 227 KB */
+constexpr int kCbcStages = 3;                /* boxes in flight per warp: no stall on the store of the previous slab */
+constexpr int kCbcTmaMaxWarps = 16;          /* 128 KB tables + 16 x 6 KB staging fits 227 KB */
+constexpr int kCbcWarpSmem = kCbcStages * kBoxBytes + kCbcStages * 8;
+
+__device__ __forceinline__ void tma_store_wait_read_1()
+{
+    asm volatile("cp.async.bulk.wait_group.read 1;" ::: "memory");
+}
 
 template <int NR, bool CFB>
 __global__ void __launch_bounds__(kCbcTmaMaxWarps * 32, 1)
@@ -537,9 +544,9 @@ aes_cbc_enc_batch_tma_kernel(const __grid_constant__ AesSched ks, const __grid_c
     fill_tables<false>(smem);
     const uint32_t lane = threadIdx.x & 31u, warp = threadIdx.x >> 5, warps = blockDim.x >> 5;
     Tb tb = { smem_base_u32(smem), lane * 4u };
-    const uint32_t stage = tb.base + kEncSmemBytes + warp * (2 * kBoxBytes);
-    const uint32_t bar = tb.base + kEncSmemBytes + warps * (2 * kBoxBytes) + warp * 16;
-    if (lane == 0) { mbar_init(bar, 1); mbar_init(bar + 8, 1); }
+    const uint32_t stage = tb.base + kEncSmemBytes + warp * (kCbcStages * kBoxBytes);
+    const uint32_t bar = tb.base + kEncSmemBytes + warps * (kCbcStages * kBoxBytes) + warp * (kCbcStages * 8);
+    if (lane == 0) for (int i = 0; i < kCbcStages; i++) mbar_init(bar + 8 * i, 1);
     asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
     __syncthreads();
     asm volatile("" : "+r"(tb.lane4));
@@ -554,21 +561,19 @@ aes_cbc_enc_batch_tma_kernel(const __grid_constant__ AesSched ks, const __grid_c
         const uint64_t m = mg * 32 + lane;
         const bool live = m < a.n_msgs;
         const uint32_t row0 = (uint32_t)(mg * 32);
-        if (lane == 0) {
+        if (lane == 0) {                                   /* two boxes ahead */
             mbar_expect_tx(bar, kBoxBytes);
             tma_load_2d(stage, &tm_in, 0, row0, bar);
+            if (n_slabs > 1) {
+                mbar_expect_tx(bar + 8, kBoxBytes);
+                tma_load_2d(stage + kBoxBytes, &tm_in, kSlab, row0, bar + 8);
+            }
         }
         uint4 c = make_uint4(0, 0, 0, 0);
         if (live) c = a.ivs[m];
+        uint32_t buf = 0;
         for (uint32_t k = 0; k < n_slabs; k++) {
-            const uint32_t buf = k & 1u;
             const uint32_t sbuf = stage + buf * kBoxBytes;
-            if (lane == 0 && k + 1 < n_slabs) {
-                tma_store_wait_read();
-                mbar_expect_tx(bar + 8 * (buf ^ 1u), kBoxBytes);
-                tma_load_2d(stage + (buf ^ 1u) * kBoxBytes, &tm_in, (k + 1) * kSlab, row0, bar + 8 * (buf ^ 1u));
-            }
-            __syncwarp();
             mbar_wait(bar + 8 * buf, (phases >> buf) & 1u);
             phases ^= 1u << buf;
             const uint32_t valid = (uint32_t)(msg_len - (uint64_t)k * kSlab < kSlab ? msg_len - (uint64_t)k * kSlab : kSlab);
@@ -586,10 +591,22 @@ aes_cbc_enc_batch_tma_kernel(const __grid_constant__ AesSched ks, const __grid_c
             }
             asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
             __syncwarp();
-            if (lane == 0) tma_store_2d(&tm_out, k * kSlab, row0, sbuf);
+            if (lane == 0) {
+                tma_store_2d(&tm_out, k * kSlab, row0, sbuf);
+                if (k + 2 < n_slabs) {
+                    /* slab k+2 goes into the buffer slab k-1 was stored from: that store (issued a
+                     * whole slab ago) must have left shared memory; the one just issued may still run */
+                    const uint32_t nb = buf == 0 ? 2u : buf - 1u;
+                    tma_store_wait_read_1();
+                    mbar_expect_tx(bar + 8 * nb, kBoxBytes);
+                    tma_load_2d(stage + nb * kBoxBytes, &tm_in, (k + 2) * kSlab, row0, bar + 8 * nb);
+                }
+            }
+            buf = buf == kCbcStages - 1 ? 0u : buf + 1u;
         }
-        if (lane == 0) tma_store_wait_read();
+        if (lane == 0) tma_store_wait_read();              /* all buffers reusable by the next message group */
         __syncwarp();
+        /* the next group starts at buffer 0 again; `phases` keeps each buffer's barrier parity */
         if (a.ivs_out && live) a.ivs_out[m] = c;     /* iv <- last ciphertext block (aes.c:807) */
     }
     if (lane == 0) tma_store_wait_all();
@@ -704,12 +721,12 @@ int launch_cbc_enc(const AesSched &ks, const CbcEncArgs &a, cudaStream_t st)
         if (warps < 1) warps = 1;
         const uint64_t ctas = (groups + warps - 1) / warps;
         const int grid = (int)(ctas < (uint64_t)sms ? ctas : (uint64_t)sms);
-        const int smem = kEncSmemBytes + (int)warps * (2 * kBoxBytes + 16);
+        const int smem = kEncSmemBytes + (int)warps * kCbcWarpSmem;
         CUtensorMap tin, tout;
         int rc = make_row_tensor_map(&tin, a.in, a.n_msgs, msg_len);
         if (rc) return rc;
         if ((rc = make_row_tensor_map(&tout, a.out, a.n_msgs, msg_len))) return rc;
-        if ((rc = set_smem(aes_cbc_enc_batch_tma_kernel<NR, CFB>, kEncSmemBytes + kCbcTmaMaxWarps * (2 * kBoxBytes + 16)))) return rc;
+        if ((rc = set_smem(aes_cbc_enc_batch_tma_kernel<NR, CFB>, kEncSmemBytes + kCbcTmaMaxWarps * kCbcWarpSmem))) return rc;
         aes_cbc_enc_batch_tma_kernel<NR, CFB><<<grid, (int)warps * 32, smem, st>>>(ks, a, tin, tout);
         BC_CUDA(cudaGetLastError(), "aes_cbc_enc_batch_tma_kernel launch");
         return BC_OK;
