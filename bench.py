@@ -245,6 +245,9 @@ def other_workloads(pkg, L, d_in, d_out, st, hbm_peak):
             e256.ctypes.data, nr, n_msgs, 65536, d_iv.data_ptr(), None, ip, op, st)), 2.0 * n + 16.0 * n_msgs),
         "rc4_batched_1m_keys_x_4k": (lambda: pkg.check(L.bc_arc4_batch_dev(
             n_streams, d_keys.data_ptr(), 16, 4096, ip, op, None, None, st)), 2.0 * n + 16.0 * n_streams),
+        # in == out (how the reference itself calls rc4_crypt, test.c:163-166): the TMA unit XORs the keystream into HBM
+        "rc4_batched_1m_keys_x_4k_in_place": (lambda: pkg.check(L.bc_arc4_batch_dev(
+            n_streams, d_keys.data_ptr(), 16, 4096, op, op, None, None, st)), 2.0 * n + 16.0 * n_streams),
     }
     out = {}
     for name, (fn, traffic) in runs.items():

@@ -22,6 +22,7 @@
 #include <cuda.h>
 #include <cuda_runtime.h>
 #include <stdint.h>
+#include <stdlib.h>
 
 #include "bulkcipher.h"
 #include "bc_internal.h"
@@ -219,6 +220,7 @@ struct Rc4TmaArgs {
     uint32_t keylen;
     uint64_t length;
     uint32_t has_in;
+    uint32_t xor_in_place;       /* in == out: keystream boxes are XORed into global memory by the TMA unit */
     const unsigned char *ctx_in;
     unsigned char *ctx_out;
 };
@@ -276,7 +278,7 @@ rc4_batch_tma_kernel(const __grid_constant__ Rc4TmaArgs a, const __grid_constant
         const uint32_t row0 = (uint32_t)(sg * 32);
 
         /* first box on its way while the key schedule runs */
-        if (a.has_in && n_slabs && lane == 0) {
+        if (a.has_in && !a.xor_in_place && n_slabs && lane == 0) {
             mbar_expect_tx(bar, kBoxBytes);
             tma_load_2d(stage, &tm_in, 0, row0, bar);
         }
@@ -331,13 +333,13 @@ rc4_batch_tma_kernel(const __grid_constant__ Rc4TmaArgs a, const __grid_constant
             const uint32_t sbuf = stage + buf * kBoxBytes;
             if (lane == 0 && k + 1 < n_slabs) {
                 tma_store_wait_read();               /* the other buffer's last store has left shared memory */
-                if (a.has_in) {
+                if (a.has_in && !a.xor_in_place) {
                     mbar_expect_tx(bar + 8 * (buf ^ 1u), kBoxBytes);
                     tma_load_2d(stage + (buf ^ 1u) * kBoxBytes, &tm_in, (k + 1) * kSlab, row0, bar + 8 * (buf ^ 1u));
                 }
             }
             __syncwarp();
-            if (a.has_in) { mbar_wait(bar + 8 * buf, (phases >> buf) & 1u); phases ^= 1u << buf; }
+            if (a.has_in && !a.xor_in_place) { mbar_wait(bar + 8 * buf, (phases >> buf) & 1u); phases ^= 1u << buf; }
             const uint32_t valid = (uint32_t)(a.length - (uint64_t)k * kSlab < kSlab ? a.length - (uint64_t)k * kSlab : kSlab);
 #pragma unroll
             for (uint32_t c = 0; c < 4; c++) {
@@ -353,14 +355,17 @@ rc4_batch_tma_kernel(const __grid_constant__ Rc4TmaArgs a, const __grid_constant
                     }
                     const uint32_t sa = sbuf + row_off + ((c ^ swz) << 4);
                     uint4 d = make_uint4(0, 0, 0, 0);
-                    if (a.has_in) d = lds128(sa);
+                    if (a.has_in && !a.xor_in_place) d = lds128(sa);
                     d.x ^= w[0]; d.y ^= w[1]; d.z ^= w[2]; d.w ^= w[3];
                     sts128(sa, d);
                 }
             }
             asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
             __syncwarp();
-            if (lane == 0) tma_store_2d(&tm_out, k * kSlab, row0, sbuf);
+            if (lane == 0) {
+                if (a.xor_in_place) tma_reduce_xor_2d(&tm_out, k * (kSlab / 4), row0, sbuf);
+                else tma_store_2d(&tm_out, k * kSlab, row0, sbuf);
+            }
         }
         if (lane == 0) tma_store_wait_read();        /* both buffers reusable by the next stream group */
         __syncwarp();
@@ -459,10 +464,11 @@ extern "C" int bc_arc4_batch_dev(size_t n_streams, const void *d_keys, unsigned 
         t.keylen = keylen;
         t.length = length;
         t.has_in = d_in != nullptr;
+        t.xor_in_place = (d_in != nullptr && d_in == d_out && !getenv("BULKCIPHER_NO_TMA_REDUCE"));
         t.ctx_in = (const unsigned char *)d_ctx_in;
         t.ctx_out = (unsigned char *)d_ctx_out;
         CUtensorMap tin, tout;
-        int rc = make_row_tensor_map(&tout, d_out, n_streams, length);
+        int rc = make_row_tensor_map(&tout, d_out, n_streams, length, t.xor_in_place != 0);
         if (rc) return rc;
         if ((rc = make_row_tensor_map(&tin, d_in ? d_in : d_out, n_streams, length))) return rc;
         return key16 ? launch_rc4_tma<true>(t, tin, tout, st) : launch_rc4_tma<false>(t, tin, tout, st);

@@ -64,6 +64,14 @@ __device__ __forceinline__ void tma_store_2d(const CUtensorMap *tm, uint32_t c0,
     asm volatile("cp.async.bulk.commit_group;" ::: "memory");
 }
 
+/* global[box] ^= shared[box]: the XOR happens in the memory system (L2), nothing is loaded */
+__device__ __forceinline__ void tma_reduce_xor_2d(const CUtensorMap *tm, uint32_t c0, uint32_t c1, uint32_t src)
+{
+    asm volatile("cp.reduce.async.bulk.tensor.2d.global.shared::cta.xor.tile.bulk_group [%0, {%1, %2}], [%3];"
+                 :: "l"(tm), "r"(c0), "r"(c1), "r"(src) : "memory");
+    asm volatile("cp.async.bulk.commit_group;" ::: "memory");
+}
+
 __device__ __forceinline__ void tma_store_wait_read()
 {
     asm volatile("cp.async.bulk.wait_group.read 0;" ::: "memory");
@@ -90,7 +98,7 @@ typedef CUresult (*EncodeTiledFn)(CUtensorMap *, CUtensorMapDataType, cuuint32_t
                                   const cuuint64_t *, const cuuint32_t *, const cuuint32_t *, CUtensorMapInterleave,
                                   CUtensorMapSwizzle, CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
 
-int make_row_tensor_map(CUtensorMap *tm, const void *ptr, uint64_t n_rows, uint64_t row_bytes)
+int make_row_tensor_map(CUtensorMap *tm, const void *ptr, uint64_t n_rows, uint64_t row_bytes, bool as_u32 = false)
 {
     static EncodeTiledFn encode = nullptr;
     if (!encode) {
@@ -100,11 +108,12 @@ int make_row_tensor_map(CUtensorMap *tm, const void *ptr, uint64_t n_rows, uint6
         if (!fn || q != cudaDriverEntryPointSuccess) { bc_set_error("cuTensorMapEncodeTiled is not available"); return BC_ERR_CUDA; }
         encode = (EncodeTiledFn)fn;
     }
-    const cuuint64_t dims[2] = { (cuuint64_t)row_bytes, (cuuint64_t)n_rows };
+    /* as_u32: same bytes described as 32-bit elements (bitwise TMA reductions need a 32-bit type) */
+    const cuuint64_t dims[2] = { (cuuint64_t)(as_u32 ? row_bytes / 4 : row_bytes), (cuuint64_t)n_rows };
     const cuuint64_t strides[1] = { (cuuint64_t)row_bytes };
-    const cuuint32_t box[2] = { (cuuint32_t)kSlab, 32u };
+    const cuuint32_t box[2] = { (cuuint32_t)(as_u32 ? kSlab / 4 : kSlab), 32u };
     const cuuint32_t estr[2] = { 1u, 1u };
-    CUresult r = encode(tm, CU_TENSOR_MAP_DATA_TYPE_UINT8, 2, const_cast<void *>(ptr), dims, strides, box, estr,
+    CUresult r = encode(tm, as_u32 ? CU_TENSOR_MAP_DATA_TYPE_UINT32 : CU_TENSOR_MAP_DATA_TYPE_UINT8, 2, const_cast<void *>(ptr), dims, strides, box, estr,
                         CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_64B, CU_TENSOR_MAP_L2_PROMOTION_NONE,
                         CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
     if (r != CUDA_SUCCESS) { bc_set_error("cuTensorMapEncodeTiled failed (CUresult %d)", (int)r); return BC_ERR_CUDA; }

@@ -63,6 +63,8 @@ def main():
     d_keys = torch.randint(0, 256, (n_streams * 16,), dtype=torch.uint8, device="cuda")
     runs.append(("rc4_batch_4k", n, lambda: pkg.check(L.bc_arc4_batch_dev(n_streams, d_keys.data_ptr(), 16, 4096, d_in.data_ptr(), d_out.data_ptr(), None, None, st))))
 
+    runs.append(("rc4_batch_4k_inplace", n, lambda: pkg.check(L.bc_arc4_batch_dev(n_streams, d_keys.data_ptr(), 16, 4096, d_out.data_ptr(), d_out.data_ptr(), None, None, st))))
+
     for name, nbytes, fn in runs:
         if args.only and args.only not in name:
             continue
