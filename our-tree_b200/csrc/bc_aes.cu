@@ -444,7 +444,11 @@ aes_blocks_kernel(const __grid_constant__ AesSched ks, const __grid_constant__ B
                 c.z = __byte_perm(c.z, 0, 0x0123); c.w = __byte_perm(c.w, 0, 0x0123);
             }
             uint4 prev = make_uint4(0, 0, 0, 0);
-            if (CHAIN) {                           /* C_{i-1}: the lane to the left, lane 0 from the previous row */
+            if (CHAIN && a.in != a.out) {
+                /* out of place nothing overwrites the input: C_{i-1} is one more (cache-resident) load,
+                 * cheaper on the shared data pipe than eight shuffles per row */
+                if (live) prev = (b == 0) ? a.iv : a.in[b - 1];
+            } else if (CHAIN) {                    /* in place: the lane to the left, lane 0 from the previous row */
                 prev.x = __shfl_up_sync(0xffffffffu, c.x, 1);
                 prev.y = __shfl_up_sync(0xffffffffu, c.y, 1);
                 prev.z = __shfl_up_sync(0xffffffffu, c.z, 1);
