@@ -24,12 +24,19 @@
  *    cut into groups of 256 consecutive counter values (only the last counter
  *    byte varies inside a group), so 15 of round 1's 16 lookups and 12 of
  *    round 2's 16 are per-group constants (AES_FROUND index pattern,
- *    aes.c:603-621): 133 instead of 160 lookups per AES-128 block.  Lane i of
- *    a warp precomputes the constants of the warp's i-th group; they are
- *    broadcast with shuffles.
- *  - Persistent grid: one 512-thread CTA per SM (tables fill 128 KB), warps
- *    stride over 4 KiB row-groups; global traffic is 128-bit, coalesced
- *    (a warp row = 512 contiguous bytes), streaming (evict-first) hints.
+ *    aes.c:603-621), and round 1's 16th is a per-lane constant for the whole
+ *    kernel: 132 instead of 160 lookups per AES-128 block.  Lane i of a warp
+ *    precomputes the constants of the warp's i-th group; they are broadcast
+ *    with shuffles.
+ *  - Persistent grid: one 1024-thread CTA per SM (tables fill 128 KB; 32 warps
+ *    at 64 registers hide the LDS latency), warps stride over 4 KiB
+ *    row-groups; global traffic is 128-bit, coalesced (a warp row = 512
+ *    contiguous bytes), streaming (evict-first) hints.
+ *  - Batched CBC/CFB encrypt (one chain per lane) stages its rows through
+ *    shared memory with 2-D TMA boxes (bc_tma.cuh).
+ *
+ * The BC_CTR_* / BC_BLK_THREADS macros are the knobs of the A/B runs recorded in
+ * profiles/r1_summary.md; the defaults are the measured best.
  */
 #include <cuda_runtime.h>
 #include <stdint.h>
