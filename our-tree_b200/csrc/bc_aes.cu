@@ -284,7 +284,9 @@ aes_ctr_kernel(const __grid_constant__ AesSched ks, const __grid_constant__ CtrA
 #endif
 
     const uint64_t nb_all = a.nblocks + (a.tail ? 1u : 0u);
-    const uint64_t warp_gid = (uint64_t)blockIdx.x * WARPS + (threadIdx.x >> 5);
+    /* work items go round-robin over CTAs first, then over a CTA's warps: every SM gets the
+     * same number of items to within one (the warps of an SM share one data pipe anyway) */
+    const uint64_t warp_gid = blockIdx.x + (uint64_t)gridDim.x * (threadIdx.x >> 5);
     const uint64_t n_warps = (uint64_t)gridDim.x * WARPS;
 
     for (uint64_t chunk = warp_gid; chunk < a.n_chunks; chunk += n_warps) {
@@ -429,7 +431,7 @@ aes_blocks_kernel(const __grid_constant__ AesSched ks, const __grid_constant__ B
     Tb tb = { smem_base_u32(smem), lane * 4u };
     asm volatile("" : "+r"(tb.lane4));
 
-    const uint64_t warp_gid = (uint64_t)blockIdx.x * kWarps + (threadIdx.x >> 5);
+    const uint64_t warp_gid = blockIdx.x + (uint64_t)gridDim.x * (threadIdx.x >> 5);   /* round-robin over CTAs first */
     const uint64_t n_warps = (uint64_t)gridDim.x * kWarps;
 
     for (uint64_t g = warp_gid; g < a.n_groups; g += n_warps) {
@@ -568,7 +570,7 @@ aes_cbc_enc_batch_tma_kernel(const __grid_constant__ AesSched ks, const __grid_c
     const uint64_t n_groups = (a.n_msgs + 31) / 32;
     const uint64_t n_warps = (uint64_t)gridDim.x * warps;
 
-    for (uint64_t mg = (uint64_t)blockIdx.x * warps + warp; mg < n_groups; mg += n_warps) {
+    for (uint64_t mg = blockIdx.x + (uint64_t)gridDim.x * warp; mg < n_groups; mg += n_warps) {
         const uint64_t m = mg * 32 + lane;
         const bool live = m < a.n_msgs;
         const uint32_t row0 = (uint32_t)(mg * 32);

@@ -272,7 +272,7 @@ rc4_batch_tma_kernel(const __grid_constant__ Rc4TmaArgs a, const __grid_constant
     const uint64_t n_warps = (uint64_t)gridDim.x * kTmaWarps;
     const uint32_t n_slabs = (uint32_t)((a.length + kSlab - 1) / kSlab);
 
-    for (uint64_t sg = (uint64_t)blockIdx.x * kTmaWarps + warp; sg < n_groups; sg += n_warps) {
+    for (uint64_t sg = blockIdx.x + (uint64_t)gridDim.x * warp; sg < n_groups; sg += n_warps) {   /* round-robin over CTAs first */
         const uint64_t s = sg * 32 + lane;
         const bool live = s < a.n_streams;
         const uint32_t row0 = (uint32_t)(sg * 32);
