@@ -5,7 +5,7 @@ import torch
 
 
 def to_dev(a):
-    return torch.from_numpy(np.ascontiguousarray(a, dtype=np.uint8)).cuda()
+    return torch.from_numpy(np.array(a, dtype=np.uint8, copy=True)).cuda()
 
 
 def stream():

@@ -329,3 +329,46 @@ def test_reference_objects_agree_when_present(pkg, ref):
             s = ref.packed_schedule(key, ENC)
             assert np.array_equal(pkg.AES_CTR_encrypt(data, b"HloEelAS", b"315A", s, nr),
                                   ref.aesni_ctr(s, nr, b"HloEelAS", b"315A", data))
+
+
+def test_no_writes_outside_output(pkg, orc):
+    """compute-sanitizer is closed on this pool, so bounds are checked the plain way: every
+    kernel writes into the middle of a canary-filled buffer (sizes that end inside a warp row, a
+    row-group and a TMA box) and the canaries on both sides must survive."""
+    import torch
+    rng = np.random.default_rng(404)
+    key = rng.integers(0, 256, 32, dtype=np.uint8).tobytes()
+    rke, nr = G.sched(pkg, key, ENC)
+    rkd, _ = G.sched(pkg, key, DEC)
+    L = pkg.lib()
+    guard = 4096
+    for n in (16, 16 * 31, 16 * 33, 4096 - 16, 4096 + 16, 16 * 257, 65536 + 48):
+        data = rng.integers(0, 256, n, dtype=np.uint8)
+        d_in = G.to_dev(data)
+        iv = bytes(range(16))
+        d_iv = G.to_dev(np.frombuffer(iv, np.uint8))
+
+        def run(fn):
+            buf = torch.full((n + 2 * guard,), 0xA5, dtype=torch.uint8, device="cuda")
+            fn(buf.data_ptr() + guard)
+            h = G.host(buf)
+            assert (h[:guard] == 0xA5).all() and (h[guard + n:] == 0xA5).all(), (fn.__name__, n)
+            return h[guard:guard + n]
+
+        def ecb(p): pkg.check(L.bc_aes_ecb_dev(rke.ctypes.data, nr, ENC, d_in.data_ptr(), p, n, G.stream()))
+        def ecbd(p): pkg.check(L.bc_aes_ecb_dev(rkd.ctypes.data, nr, DEC, d_in.data_ptr(), p, n, G.stream()))
+        def cbcd(p): pkg.check(L.bc_aes_cbc_decrypt_dev(rkd.ctypes.data, nr, iv, d_in.data_ptr(), p, n, G.stream()))
+        def cfbd(p): pkg.check(L.bc_aes_cfb128_decrypt_dev(rke.ctypes.data, nr, iv, d_in.data_ptr(), p, n, G.stream()))
+        def ctr(p): pkg.check(L.bc_aes_ctr_dev(rke.ctypes.data, nr, iv, 128, 5, d_in.data_ptr(), p, n, None, G.stream()))
+        def cbce(p): pkg.check(L.bc_aes_cbc_encrypt_batch_dev(rke.ctypes.data, nr, 1, n, d_iv.data_ptr(), None, d_in.data_ptr(), p, G.stream()))
+        def cfbe(p): pkg.check(L.bc_aes_cfb128_encrypt_batch_dev(rke.ctypes.data, nr, 1, n, d_iv.data_ptr(), None, d_in.data_ptr(), p, G.stream()))
+        def rc4(p): pkg.check(L.bc_arc4_batch_dev(n // 16, d_in.data_ptr(), 16, 16, d_in.data_ptr(), p, None, None, G.stream()))
+
+        assert np.array_equal(run(ecb), orc.aes_ecb(key, ENC, data))
+        assert np.array_equal(run(ecbd), orc.aes_ecb(key, DEC, data))
+        assert np.array_equal(run(cbcd), orc.aes_cbc(key, DEC, iv, data)[1])
+        assert np.array_equal(run(cfbd), orc.aes_cfb128(key, DEC, iv, data)[0])
+        assert np.array_equal(run(cbce), orc.aes_cbc(key, ENC, iv, data)[1])
+        assert np.array_equal(run(cfbe), orc.aes_cfb128(key, ENC, iv, data)[0])
+        run(ctr)
+        assert np.array_equal(run(rc4), orc.arc4_batch(data, 16, data, 16))
