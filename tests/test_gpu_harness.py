@@ -42,3 +42,17 @@ def test_aes_gpu_cpp_facade():
     out = run([os.path.join(BUILD, "aes_gpu_facade_test")])
     assert "all outputs verified" in out and "MISMATCH" not in out
     assert out.count("FIPS-197") == 3 and "Invalid AES key size" in out
+
+
+@pytest.mark.skipif(not os.environ.get("BULKCIPHER_RUN_REF_HARNESS"), reason="minutes-long; set BULKCIPHER_RUN_REF_HARNESS=1")
+def test_reference_harness_binaries_relinked():
+    """The reference's own aes-modes/test.c and test.c, compiled unmodified against include/ and linked
+    with libbulkcipher.so (`make ref-harness`): they must run to completion; test.c ends with the
+    reference's arc4_self_test, whose three 'passed' lines therefore come from the GPU path."""
+    aes, rc4 = os.path.join(BUILD, "ref_aes_modes_test"), os.path.join(BUILD, "ref_rc4_test")
+    if not (os.path.exists(aes) and os.path.exists(rc4)):
+        pytest.skip("ref harness binaries not built (no reference tree where this was built)")
+    p = subprocess.run([aes], capture_output=True, text=True, timeout=1800)
+    assert p.returncode == 0 and "AESNI CTR, 1048576000, 8," in p.stdout, p.stdout[-2000:] + p.stderr[-2000:]
+    p = subprocess.run([rc4], capture_output=True, text=True, timeout=3000)
+    assert p.returncode == 0 and p.stdout.count("passed") == 3, p.stdout[-2000:] + p.stderr[-2000:]
