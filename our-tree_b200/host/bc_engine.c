@@ -17,6 +17,7 @@
 #include <stdio.h>
 #include <stdlib.h>
 #include <string.h>
+#include <unistd.h>
 
 #include <cuda_runtime_api.h>
 
@@ -30,6 +31,7 @@
  * BULKCIPHER_CHUNK_MIB and BULKCIPHER_SLOTS override them before the first call. */
 static size_t g_chunk = (size_t)64 << 20;
 static int    g_slots = 3;
+static size_t g_pageable_chunk = (size_t)16 << 20;   /* cap for pageable (host-in-the-loop) transfers */
 #define BC_SLOTS       g_slots
 #define BC_CHUNK_BYTES g_chunk
 #define BC_MAX_SCRATCH 8
@@ -96,6 +98,8 @@ static void init_locks(void)
 {
     const char *e = getenv("BULKCIPHER_CHUNK_MIB");
     if (e && atoi(e) >= 1 && atoi(e) <= 1024) g_chunk = (size_t)atoi(e) << 20;
+    e = getenv("BULKCIPHER_PAGEABLE_CHUNK_MIB");
+    if (e && atoi(e) >= 1 && atoi(e) <= 1024) g_pageable_chunk = (size_t)atoi(e) << 20;
     e = getenv("BULKCIPHER_SLOTS");
     if (e && atoi(e) >= 2 && atoi(e) <= BC_MAX_SLOTS) g_slots = atoi(e);
     for (int i = 0; i < BC_MAX_DEVICES; i++) {
@@ -229,6 +233,92 @@ int bc_device_sync(void)
     return BC_OK;
 }
 
+/* ------------------------------------------------------ parallel staging copy */
+
+/* Pageable caller memory has to pass through pinned staging buffers, and one core's memcpy
+ * (~10 GB/s) is far below the PCIe rate.  A small pool of helper threads splits every large
+ * staging copy; the calling thread takes a share too.  Pure data movement: no cipher work is
+ * ever done on the host.  BULKCIPHER_COPY_THREADS overrides the helper count (0 = none). */
+#define BC_MAX_COPY_THREADS 16
+#define BC_PAR_COPY_MIN ((size_t)4 << 20)
+
+typedef struct { unsigned char *dst; const unsigned char *src; size_t n; } bc_copy_job;
+
+static pthread_mutex_t g_copy_user = PTHREAD_MUTEX_INITIALIZER;   /* one parallel copy at a time */
+static pthread_mutex_t g_copy_mu   = PTHREAD_MUTEX_INITIALIZER;
+static pthread_cond_t  g_copy_work = PTHREAD_COND_INITIALIZER;
+static pthread_cond_t  g_copy_done = PTHREAD_COND_INITIALIZER;
+static bc_copy_job     g_copy_jobs[BC_MAX_COPY_THREADS];
+static unsigned        g_copy_gen;
+static int             g_copy_pending;
+static int             g_copy_threads = -1;                       /* -1: pool not started yet */
+
+static void *copy_worker(void *arg)
+{
+    const int id = (int)(intptr_t)arg;
+    unsigned seen = 0;
+    for (;;) {
+        pthread_mutex_lock(&g_copy_mu);
+        while (seen == g_copy_gen) pthread_cond_wait(&g_copy_work, &g_copy_mu);
+        seen = g_copy_gen;
+        const bc_copy_job job = g_copy_jobs[id];
+        pthread_mutex_unlock(&g_copy_mu);
+        if (job.n) memcpy(job.dst, job.src, job.n);
+        pthread_mutex_lock(&g_copy_mu);
+        if (--g_copy_pending == 0) pthread_cond_signal(&g_copy_done);
+        pthread_mutex_unlock(&g_copy_mu);
+    }
+    return NULL;
+}
+
+/* called with g_copy_user held */
+static void copy_pool_start(void)
+{
+    long want = sysconf(_SC_NPROCESSORS_ONLN) / 2;
+    const char *e = getenv("BULKCIPHER_COPY_THREADS");
+    if (e) want = atoi(e);
+    if (want > 8 && !e) want = 8;
+    if (want > BC_MAX_COPY_THREADS) want = BC_MAX_COPY_THREADS;
+    if (want < 0) want = 0;
+    int started = 0;
+    for (long i = 0; i < want; i++) {
+        pthread_t th;
+        pthread_attr_t at;
+        pthread_attr_init(&at);
+        pthread_attr_setdetachstate(&at, PTHREAD_CREATE_DETACHED);
+        if (pthread_create(&th, &at, copy_worker, (void *)(intptr_t)started) != 0) { pthread_attr_destroy(&at); break; }
+        pthread_attr_destroy(&at);
+        started++;
+    }
+    g_copy_threads = started;
+}
+
+static void par_memcpy(void *dst, const void *src, size_t n)
+{
+    if (n < BC_PAR_COPY_MIN) { memcpy(dst, src, n); return; }
+    pthread_mutex_lock(&g_copy_user);
+    if (g_copy_threads < 0) copy_pool_start();
+    const int w = g_copy_threads;
+    if (w == 0) { pthread_mutex_unlock(&g_copy_user); memcpy(dst, src, n); return; }
+    /* w + 1 shares of whole 4 KiB pages; the caller takes the last (and the remainder) */
+    const size_t share = (n / (size_t)(w + 1)) & ~(size_t)4095;
+    pthread_mutex_lock(&g_copy_mu);
+    for (int i = 0; i < w; i++) {
+        g_copy_jobs[i].dst = (unsigned char *)dst + share * (size_t)i;
+        g_copy_jobs[i].src = (const unsigned char *)src + share * (size_t)i;
+        g_copy_jobs[i].n = share;
+    }
+    g_copy_pending = w;
+    g_copy_gen++;
+    pthread_cond_broadcast(&g_copy_work);
+    pthread_mutex_unlock(&g_copy_mu);
+    memcpy((unsigned char *)dst + share * (size_t)w, (const unsigned char *)src + share * (size_t)w, n - share * (size_t)w);
+    pthread_mutex_lock(&g_copy_mu);
+    while (g_copy_pending) pthread_cond_wait(&g_copy_done, &g_copy_mu);
+    pthread_mutex_unlock(&g_copy_mu);
+    pthread_mutex_unlock(&g_copy_user);
+}
+
 /* ------------------------------------------------------- pipeline plumbing */
 
 static int dev_prepare(bc_dev **out)
@@ -294,7 +384,7 @@ static int slot_retire(bc_slot *s)
 {
     BC_CUDA(cudaEventSynchronize(s->done), "cudaEventSynchronize");
     if (s->pend_dst) {
-        memcpy(s->pend_dst, s->pin_out, s->pend_len);
+        par_memcpy(s->pend_dst, s->pin_out, s->pend_len);
         s->pend_dst = NULL;
     }
     return BC_OK;
@@ -355,7 +445,7 @@ static int run_pipeline(bc_dev *d, const unsigned char *in, unsigned char *out, 
         if ((in && !in_pinned) || !out_pinned) { if ((rc = slot_ensure_pinned(s))) break; }
         if (in) {                                  /* in == NULL: the kernel only produces output */
             const unsigned char *src = in + off;
-            if (!in_pinned) { memcpy(s->pin_in, src, n); src = s->pin_in; }
+            if (!in_pinned) { par_memcpy(s->pin_in, src, n); src = s->pin_in; }
             e = cudaMemcpyAsync(s->d_buf, src, n, cudaMemcpyHostToDevice, s->stream);
             if (e != cudaSuccess) { rc = bc_cuda_fail((int)e, "cudaMemcpyAsync H2D"); break; }
         }
@@ -379,13 +469,17 @@ static int run_pipeline(bc_dev *d, const unsigned char *in, unsigned char *out, 
 }
 
 /* Chunk size for a transfer of nbytes: the full granule for big buffers, about an eighth of
- * the buffer (whole MiB, at least 4 MiB) for smaller ones so that copies still overlap. */
-static size_t pick_chunk(size_t nbytes)
+ * the buffer (whole MiB, at least 4 MiB) for smaller ones so that copies still overlap.
+ * Pageable buffers keep the host in the loop (staging copies between the waits), where smaller
+ * chunks interleave better: capped at g_pageable_chunk (tools/e2e_probe.py ... pageable). */
+static size_t pick_chunk(size_t nbytes, const void *in, const void *out)
 {
-    if (nbytes >= 8 * BC_CHUNK_BYTES) return BC_CHUNK_BYTES;
+    size_t cap = BC_CHUNK_BYTES;
+    if ((in && classify(in) != 1) || classify(out) != 1) cap = g_pageable_chunk < cap ? g_pageable_chunk : cap;
+    if (nbytes >= 8 * cap) return cap;
     size_t c = ((nbytes / 8) + ((size_t)1 << 20) - 1) & ~(((size_t)1 << 20) - 1);
     if (c < ((size_t)4 << 20)) c = (size_t)4 << 20;
-    return c < BC_CHUNK_BYTES ? c : BC_CHUNK_BYTES;
+    return c < cap ? c : cap;
 }
 
 static int check_host_args(const uint32_t *rk, int nr, const void *in, const void *out, size_t nbytes)
@@ -435,7 +529,7 @@ int bc_aes_ctr_host(const uint32_t *rk, int nr, const unsigned char counter[16],
     pthread_mutex_lock(&d->lock);
     if ((rc = dev_ensure_slots(d)) == BC_OK && (rc = dev_ensure_aux(d, 16)) == BC_OK) {
         ctr_op o = { rk, nr, counter, counter_bits, first_block, nbytes, last_keystream ? d->d_aux : NULL };
-        rc = run_pipeline(d, (const unsigned char *)in, (unsigned char *)out, nbytes, pick_chunk(nbytes), ctr_chunk, &o);
+        rc = run_pipeline(d, (const unsigned char *)in, (unsigned char *)out, nbytes, pick_chunk(nbytes, in, out), ctr_chunk, &o);
         if (rc == BC_OK && last_keystream) rc = bc_memcpy_d2h(last_keystream, d->d_aux, 16);
     }
     pthread_mutex_unlock(&d->lock);
@@ -468,7 +562,7 @@ static int ecb_host(int be32, const uint32_t *rk, int nr, int mode, const void *
     pthread_mutex_lock(&d->lock);
     if ((rc = dev_ensure_slots(d)) == BC_OK) {
         ecb_op o = { rk, nr, mode, be32 };
-        rc = run_pipeline(d, (const unsigned char *)in, (unsigned char *)out, nbytes, pick_chunk(nbytes), ecb_chunk, &o);
+        rc = run_pipeline(d, (const unsigned char *)in, (unsigned char *)out, nbytes, pick_chunk(nbytes, in, out), ecb_chunk, &o);
     }
     pthread_mutex_unlock(&d->lock);
     return rc;
@@ -511,7 +605,7 @@ static int chained_decrypt_host(int cfb, const uint32_t *rk, int nr, const unsig
     }
     /* Chunk k chains from the last ciphertext block of chunk k-1.  Collect those
      * blocks first: with in == out the pipeline's D2H would overwrite them. */
-    const size_t chunk = pick_chunk(nbytes);
+    const size_t chunk = pick_chunk(nbytes, in, out);
     const size_t n_chunks = (nbytes + chunk - 1) / chunk;
     unsigned char *ivs = (unsigned char *)malloc(16 * n_chunks);
     if (!ivs) { bc_set_error("out of host memory"); return BC_ERR_BAD_ARG; }
