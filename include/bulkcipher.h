@@ -48,6 +48,8 @@ int  bc_get_device(void);
 int  bc_sm_count(void);
 
 /* ---- memory helpers for C callers (harness, multi-GPU driver) ------------ */
+/* bc_memcpy_* are synchronous copies on the legacy default stream: follow them with calls on
+ * stream NULL, or synchronise before using a non-blocking stream of your own. */
 void *bc_host_alloc(size_t bytes);            /* pinned host memory (cudaHostAlloc)   */
 void  bc_host_free(void *p);
 void *bc_dev_alloc(size_t bytes);

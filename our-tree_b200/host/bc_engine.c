@@ -830,12 +830,12 @@ static int xor_chunk(void *arg, size_t idx, size_t off, size_t n, void *d, cudaS
 {
     xor_op *o = (xor_op *)arg;
     unsigned char *d_b = o->d_b + (idx % BC_SLOTS) * BC_CHUNK_BYTES;
-    /* pageable `b` goes through a synchronous staged copy; fine for a memory-bound XOR */
-    if (o->b_pinned) BC_CUDA(cudaMemcpyAsync(d_b, o->b + off, n, cudaMemcpyHostToDevice, st), "cudaMemcpyAsync b");
-    else {
-        BC_CUDA(cudaStreamSynchronize(st), "cudaStreamSynchronize");
-        BC_CUDA(cudaMemcpy(d_b, o->b + off, n, cudaMemcpyHostToDevice), "cudaMemcpy b");
-    }
+    /* Same stream as the kernel, pinned or not: for pageable memory the runtime stages the copy
+     * and keeps it ordered inside `st`.  (A plain cudaMemcpy would run on the legacy stream, which
+     * the non-blocking pipeline streams do not wait for — its last staged piece could still be in
+     * flight when the XOR kernel starts.) */
+    (void)o->b_pinned;
+    BC_CUDA(cudaMemcpyAsync(d_b, o->b + off, n, cudaMemcpyHostToDevice, st), "cudaMemcpyAsync b");
     return bc_xor_dev(d, d_b, d, n, st);
 }
 

@@ -1,0 +1,138 @@
+"""GPU: the host-buffer pipeline (bc_*_host) on transfers that span many chunks, for pageable
+(numpy) and pinned (bc_host_alloc) memory, in place and out of place, including the rarely
+taken branches: one CBC message / one RC4 stream longer than a pipeline buffer (chained
+through iv / context), ragged CTR tails, the last-keystream output.  The device entry points
+(already pinned to the oracle by the other tests) are the expected values here, plus sampled
+windows straight from the oracle."""
+import ctypes
+
+import numpy as np
+import pytest
+
+import gpu_util as G
+
+pytestmark = pytest.mark.gpu
+ENC, DEC = 1, 0
+MIB = 1 << 20
+
+
+class Pinned:
+    def __init__(self, pkg, n):
+        self.pkg, self.n = pkg, n
+        self.ptr = pkg.lib().bc_host_alloc(n)
+        assert self.ptr, pkg.last_error()
+        self.a = np.ctypeslib.as_array((ctypes.c_ubyte * n).from_address(self.ptr))
+
+    def free(self):
+        self.pkg.lib().bc_host_free(self.ptr)
+
+
+def device_expect(pkg, fn, data, extra=0):
+    d_in = G.to_dev(data)
+    d_out = G.to_dev(np.zeros(data.size + extra, np.uint8))
+    fn(d_in, d_out)
+    return G.host(d_out)
+
+
+@pytest.mark.parametrize("pinned", [False, True])
+def test_ctr_ecb_cbc_cfb_many_chunks(pkg, orc, pinned):
+    rng = np.random.default_rng(2024)
+    L = pkg.lib()
+    n = 150 * MIB + 16 * 37           # > 8 chunks of 16 MiB (pageable) / 3 chunks of 64 MiB (pinned)
+    key = rng.integers(0, 256, 32, dtype=np.uint8).tobytes()
+    rke, nr = G.sched(pkg, key, ENC)
+    rkd, _ = G.sched(pkg, key, DEC)
+    iv = rng.integers(0, 256, 16, dtype=np.uint8).tobytes()
+    nc = bytes.fromhex("00112233445566778899aabbffffff00")
+    src = rng.integers(0, 256, n + 11, dtype=np.uint8)
+    if pinned:
+        hin, hout = Pinned(pkg, n + 11), Pinned(pkg, n + 11)
+        hin.a[:] = src
+        a_in, a_out, p_in, p_out = hin.a, hout.a, hin.ptr, hout.ptr
+    else:
+        a_in, a_out = src.copy(), np.zeros(n + 11, np.uint8)
+        p_in, p_out = a_in.ctypes.data, a_out.ctypes.data
+
+    # CTR with a ragged tail and the last keystream block
+    m = n + 11
+    want = device_expect(pkg, lambda i, o: G.ctr_dev(pkg, rke, nr, nc, i, o, m, first_block=7), np.concatenate([src, np.zeros(5, np.uint8)]))[:m]
+    last = np.zeros(16, np.uint8)
+    pkg.check(L.bc_aes_ctr_host(rke.ctypes.data, nr, nc, 128, 7, p_in, p_out, m, last.ctypes.data))
+    assert np.array_equal(a_out[:m], want)
+    w0 = 64 * MIB - 4096                                     # a window across a chunk seam, straight from the oracle
+    shifted = ((int.from_bytes(nc, "big") + 7 + w0 // 16) % (1 << 128)).to_bytes(16, "big")
+    assert np.array_equal(a_out[w0:w0 + 8192], orc.aes_ctr(key, shifted, src[w0:w0 + 8192])[0])
+    sb = orc.aes_ecb(key, ENC, ((int.from_bytes(nc, "big") + 7 + (m - 1) // 16) % (1 << 128)).to_bytes(16, "big"))
+    assert last.tobytes() == sb.tobytes()
+
+    # ECB / CBC-dec / CFB-dec out of place, then CBC-dec in place
+    for name, host_call, dev_call in (
+        ("ecb", lambda i, o: L.bc_aes_ecb_host(rke.ctypes.data, nr, ENC, i, o, n),
+         lambda i, o: G.ecb_dev(pkg, rke, nr, ENC, i, o, n)),
+        ("cbc", lambda i, o: L.bc_aes_cbc_decrypt_host(rkd.ctypes.data, nr, iv, i, o, n),
+         lambda i, o: G.cbc_dec_dev(pkg, rkd, nr, iv, i, o, n)),
+        ("cfb", lambda i, o: L.bc_aes_cfb128_decrypt_host(rke.ctypes.data, nr, iv, i, o, n),
+         lambda i, o: pkg.check(L.bc_aes_cfb128_decrypt_dev(rke.ctypes.data, nr, iv, i.data_ptr(), o.data_ptr(), n, G.stream()))),
+    ):
+        want = device_expect(pkg, dev_call, src[:n])
+        a_out[:] = 0
+        pkg.check(host_call(p_in, p_out))
+        assert np.array_equal(a_out[:n], want), name
+    want = device_expect(pkg, lambda i, o: G.cbc_dec_dev(pkg, rkd, nr, iv, i, o, n), src[:n])
+    pkg.check(L.bc_aes_cbc_decrypt_host(rkd.ctypes.data, nr, iv, p_in, p_in, n))      # in place: chunk ivs collected first
+    assert np.array_equal(a_in[:n], want)
+    if pinned:
+        hin.free()
+        hout.free()
+
+
+def test_cbc_encrypt_batch_host_shapes(pkg, orc):
+    rng = np.random.default_rng(77)
+    L = pkg.lib()
+    key = rng.integers(0, 256, 16, dtype=np.uint8).tobytes()
+    rke, nr = G.sched(pkg, key, ENC)
+    # (a) many messages, several chunks; (b) ONE message longer than a pipeline buffer (chained through iv)
+    for n_msgs, msg_len in ((3000, 64 * 1024), (2, 70 * MIB + 32)):
+        data = rng.integers(0, 256, n_msgs * msg_len, dtype=np.uint8)
+        ivs = rng.integers(0, 256, n_msgs * 16, dtype=np.uint8)
+        d_in, d_out = G.to_dev(data), G.to_dev(np.zeros_like(data))
+        d_iv, d_ivo = G.to_dev(ivs), G.to_dev(np.zeros_like(ivs))
+        G.cbc_enc_batch_dev(pkg, rke, nr, n_msgs, msg_len, d_iv, d_ivo, d_in, d_out)
+        want, want_iv = G.host(d_out), G.host(d_ivo)
+        got, got_iv = pkg.aes_cbc_encrypt_batch_host(rke, nr, ivs, data, msg_len)
+        assert np.array_equal(got, want) and np.array_equal(got_iv, want_iv), (n_msgs, msg_len)
+        m = n_msgs - 1                                        # the head of the last message, straight from the oracle
+        head = orc.aes_cbc(key, ENC, ivs[16 * m:16 * m + 16].tobytes(), data[m * msg_len:m * msg_len + 4096])[1]
+        assert np.array_equal(got[m * msg_len:m * msg_len + 4096], head)
+
+
+def test_rc4_host_shapes(pkg, orc):
+    rng = np.random.default_rng(78)
+    L = pkg.lib()
+    # (a) many streams over several chunks with contexts coming back
+    n, length = 40000, 4096
+    keys = rng.integers(0, 256, n * 16, dtype=np.uint8)
+    data = rng.integers(0, 256, n * length, dtype=np.uint8)
+    d_out = G.to_dev(np.zeros_like(data))
+    d_ctx = G.to_dev(np.zeros(n * 264, np.uint8))
+    G.arc4_dev(pkg, n, G.to_dev(keys), 16, length, G.to_dev(data), d_out, None, d_ctx)
+    got, ctx = pkg.arc4_batch_host(keys, 16, data, length, want_ctx=True)
+    assert np.array_equal(got, G.host(d_out)) and np.array_equal(ctx, G.host(d_ctx))
+    assert np.array_equal(got[-length:], orc.arc4(keys[-16:].tobytes(), data[-length:]))
+    # (b) ONE stream longer than a pipeline buffer: pieces chained through its arc4_context;
+    # the same through the drop-in arc4_setup / arc4_prep / arc4_crypt and rc4_init / rc4_crypt
+    key = b"a 70 MiB stream"
+    big = rng.integers(0, 256, 70 * MIB + 5, dtype=np.uint8)
+    want = orc.arc4(key, big)
+    out = np.zeros_like(big)
+    ctx1 = np.zeros(264, np.uint8)
+    k = np.frombuffer(key, np.uint8)
+    pkg.check(L.bc_arc4_batch_host(1, k.ctypes.data, len(key), big.size, big.ctypes.data, out.ctypes.data, None, ctx1.ctypes.data))
+    assert np.array_equal(out, want)
+    _, x, y, m = orc.arc4_keystream(key, [big.size])
+    assert (int.from_bytes(ctx1[0:4].tobytes(), "little"), int.from_bytes(ctx1[4:8].tobytes(), "little"), ctx1[8:].tobytes()) == (x, y, m)
+    c = pkg.arc4_setup(key)
+    ks = pkg.arc4_prep(c, big.size)
+    assert np.array_equal(pkg.arc4_crypt(big, ks), want) and (c.x, c.y, bytes(c.m)) == (x, y, m)
+    st = pkg.rc4_init(key)
+    assert np.array_equal(pkg.rc4_crypt(st, big), want)
