@@ -1,0 +1,111 @@
+"""GPU: corners of the C-ABI that the main parity tests do not reach — device pointers handed to
+the host-pointer entry points, calls on several CUDA streams at once (per-stream CBC scratch),
+concurrent host threads, over-long RC4 keys, zero lengths."""
+import threading
+
+import numpy as np
+import pytest
+import torch
+
+import gpu_util as G
+
+pytestmark = pytest.mark.gpu
+ENC, DEC = 1, 0
+
+
+def test_host_entry_points_accept_device_pointers(pkg, orc):
+    """bc_*_host with cudaMalloc'ed pointers: used in place on the device, no staging (aes.h header note)."""
+    rng = np.random.default_rng(11)
+    L = pkg.lib()
+    key = rng.integers(0, 256, 16, dtype=np.uint8).tobytes()
+    rke, nr = G.sched(pkg, key, ENC)
+    rkd, _ = G.sched(pkg, key, DEC)
+    data = rng.integers(0, 256, 1 << 20, dtype=np.uint8)
+    iv = bytes(range(16))
+    d_in, d_out = G.to_dev(data), G.to_dev(np.zeros_like(data))
+    last = np.zeros(16, np.uint8)
+    pkg.check(L.bc_aes_ctr_host(rke.ctypes.data, nr, iv, 128, 3, d_in.data_ptr(), d_out.data_ptr(), data.size, last.ctypes.data))
+    shifted = (int.from_bytes(iv, "big") + 3).to_bytes(16, "big")
+    want, _, _, sb = orc.aes_ctr(key, shifted, data)
+    assert np.array_equal(G.host(d_out), want) and last.tobytes() == sb
+    pkg.check(L.bc_aes_ecb_host(rke.ctypes.data, nr, ENC, d_in.data_ptr(), d_out.data_ptr(), data.size))
+    assert np.array_equal(G.host(d_out), orc.aes_ecb(key, ENC, data))
+    pkg.check(L.bc_aes_cbc_decrypt_host(rkd.ctypes.data, nr, iv, d_in.data_ptr(), d_out.data_ptr(), data.size))
+    assert np.array_equal(G.host(d_out), orc.aes_cbc(key, DEC, iv, data)[1])
+    d_iv = G.to_dev(np.frombuffer(iv * 16, np.uint8))
+    pkg.check(L.bc_aes_cbc_encrypt_batch_host(rke.ctypes.data, nr, 16, 65536, d_iv.data_ptr(), None, d_in.data_ptr(), d_out.data_ptr()))
+    want = np.concatenate([orc.aes_cbc(key, ENC, iv, data[m * 65536:(m + 1) * 65536])[1] for m in range(16)])
+    assert np.array_equal(G.host(d_out), want)
+    # the drop-in itself, device pointers straight through aes_crypt_ctr
+    rc, ctx = pkg.aes_setkey_enc(key)
+    import ctypes as C
+    off, nc, sbuf = C.c_int(0), np.frombuffer(iv, np.uint8).copy(), np.zeros(16, np.uint8)
+    rc = L.aes_crypt_ctr(C.byref(ctx), data.size, C.byref(off), nc.ctypes.data, sbuf.ctypes.data, d_in.data_ptr(), d_out.data_ptr())
+    want, woff, wnc, wsb = orc.aes_ctr(key, iv, data)
+    assert rc == 0 and np.array_equal(G.host(d_out), want) and (off.value, nc.tobytes(), sbuf.tobytes()) == (woff, wnc, wsb)
+
+
+def test_concurrent_streams_inplace_cbc(pkg, orc):
+    """In-place CBC decrypt on four streams at once: each stream gets its own boundary scratch."""
+    rng = np.random.default_rng(12)
+    L = pkg.lib()
+    key = rng.integers(0, 256, 32, dtype=np.uint8).tobytes()
+    rkd, nr = G.sched(pkg, key, DEC)
+    streams = [torch.cuda.Stream() for _ in range(4)]
+    datas = [rng.integers(0, 256, (8 + i) * (1 << 20) + 16 * i, dtype=np.uint8) for i in range(4)]
+    ivs = [rng.integers(0, 256, 16, dtype=np.uint8).tobytes() for _ in range(4)]
+    bufs = [G.to_dev(d) for d in datas]
+    torch.cuda.synchronize()
+    for rep in range(3):
+        for s, b, iv, d in zip(streams, bufs, ivs, datas):
+            pkg.check(L.bc_aes_cbc_decrypt_dev(rkd.ctypes.data, nr, iv, b.data_ptr(), b.data_ptr(), d.size, s.cuda_stream))
+        torch.cuda.synchronize()
+        if rep == 0:
+            for b, iv, d in zip(bufs, ivs, datas):
+                assert np.array_equal(G.host(b), orc.aes_cbc(key, DEC, iv, d)[1])
+
+
+def test_concurrent_host_threads(pkg, orc):
+    """The reference harness calls the API from up to 8 pthreads on slices of one buffer with one shared
+    key context (aes-modes/test.c:273-285): same here from Python threads (ctypes drops the GIL)."""
+    rng = np.random.default_rng(13)
+    key = rng.integers(0, 256, 16, dtype=np.uint8).tobytes()
+    rke, nr = G.sched(pkg, key, ENC)
+    nc = bytes.fromhex("000102030405060708090a0bfffffff5")
+    data = rng.integers(0, 256, 48 << 20, dtype=np.uint8)
+    out = np.zeros_like(data)
+    T = 8
+    per = data.size // T // 16 * 16
+    errs = []
+
+    def work(t):
+        try:
+            lo = t * per
+            hi = data.size if t == T - 1 else lo + per
+            pkg.aes_ctr_host(rke, nr, nc, data[lo:hi], first_block=lo // 16, out=out[lo:hi])
+        except Exception as e:  # noqa: BLE001
+            errs.append(e)
+
+    th = [threading.Thread(target=work, args=(t,)) for t in range(T)]
+    [t.start() for t in th]
+    [t.join() for t in th]
+    assert not errs, errs
+    assert np.array_equal(out, orc.aes_ctr(key, nc, data)[0])
+
+
+def test_rc4_long_keys_and_zero_lengths(pkg, orc):
+    rng = np.random.default_rng(14)
+    data = rng.integers(0, 256, 777, dtype=np.uint8)
+    long_key = rng.integers(0, 256, 300, dtype=np.uint8).tobytes()      # only the first 256 bytes are ever used (arc4.c:58-66)
+    ctx = pkg.arc4_setup(long_key)
+    ks = pkg.arc4_prep(ctx, data.size)
+    assert np.array_equal(pkg.arc4_crypt(data, ks), orc.arc4(long_key, data))
+    assert np.array_equal(pkg.arc4_crypt(data, ks), orc.arc4(long_key[:256], data))
+    assert pkg.arc4_prep(ctx, 0).size == 0 and pkg.arc4_crypt(b"", b"").size == 0
+    st = pkg.rc4_init(b"k")
+    assert pkg.rc4_crypt(st, b"").size == 0 and (st.index1, st.index2) == (0, 0)
+    L = pkg.lib()
+    rk = np.zeros(60, np.uint32)
+    assert L.bc_aes_ctr_host(rk.ctypes.data, 10, bytes(16), 128, 0, None, None, 0, None) == 0
+    assert L.bc_arc4_batch_host(0, None, 16, 4096, None, None, None, None) == 0
+    assert L.bc_arc4_batch_host(4, None, 16, 16, None, None, None, None) == pkg.BC_ERR_BAD_ARG
