@@ -46,6 +46,9 @@ int  bc_device_count(void);
 int  bc_set_device(int device);
 int  bc_get_device(void);
 int  bc_sm_count(void);
+/* Frees every buffer, stream and event the library owns on all devices (optional; the next
+ * call allocates again).  No other call may be in flight. */
+int  bc_shutdown(void);
 
 /* ---- memory helpers for C callers (harness, multi-GPU driver) ------------ */
 /* bc_memcpy_* are synchronous copies on the legacy default stream: follow them with calls on

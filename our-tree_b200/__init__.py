@@ -39,7 +39,7 @@ DROPIN_SYMBOLS = [
     "arc4_setup", "arc4_prep", "arc4_crypt", "arc4_self_test", "rc4_init", "rc4_crypt",
 ]
 BC_SYMBOLS = [
-    "bc_last_error", "bc_device_count", "bc_set_device", "bc_get_device", "bc_sm_count",
+    "bc_last_error", "bc_device_count", "bc_set_device", "bc_get_device", "bc_sm_count", "bc_shutdown",
     "bc_host_alloc", "bc_host_free", "bc_dev_alloc", "bc_dev_free", "bc_memcpy_h2d", "bc_memcpy_d2h",
     "bc_device_sync",
     "bc_aes_ctr_dev", "bc_aes_ecb_dev", "bc_aes_cbc_decrypt_dev", "bc_aes_cbc_encrypt_batch_dev",

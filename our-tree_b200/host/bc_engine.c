@@ -858,6 +858,56 @@ int bc_xor_host(const void *a, const void *b, void *out, size_t nbytes)
     return rc;
 }
 
+/* ------------------------------------------------------------- shutdown */
+
+/* Release everything the library owns on every device (pipeline buffers, staging, streams,
+ * events, scratch).  Optional: the resources are process-lifetime singletons; this exists for
+ * hosts that unload the library or run leak checkers.  No call may be in flight; later calls
+ * simply allocate again. */
+int bc_shutdown(void)
+{
+    pthread_once(&g_once, init_locks);
+    int prev = -1, rc = BC_OK;
+    cudaGetDevice(&prev);
+    int n = bc_device_count();
+    for (int dev = 0; dev < n && dev < BC_MAX_DEVICES; dev++) {
+        bc_dev *d = &g_dev[dev];
+        pthread_mutex_lock(&d->lock);
+        int touched = d->ready || d->d_aux;
+        for (int i = 0; i < BC_MAX_SCRATCH; i++) touched |= d->scratch[i].ptr != NULL;
+        if (touched && cudaSetDevice(dev) == cudaSuccess) {
+            cudaError_t e = cudaDeviceSynchronize();
+            if (e != cudaSuccess && rc == BC_OK) rc = bc_cuda_fail((int)e, "cudaDeviceSynchronize");
+            if (d->ready) {
+                for (int i = 0; i < BC_SLOTS; i++) {
+                    bc_slot *s = &d->slot[i];
+                    cudaFree(s->d_buf);
+                    if (s->pin_in) cudaFreeHost(s->pin_in);
+                    if (s->pin_out) cudaFreeHost(s->pin_out);
+                    cudaStreamDestroy(s->stream);
+                    cudaEventDestroy(s->done);
+                    cudaEventDestroy(d->e_h2d[i]);
+                    cudaEventDestroy(d->e_k[i]);
+                    cudaEventDestroy(d->e_d2h[i]);
+                    memset(s, 0, sizeof *s);
+                }
+                cudaStreamDestroy(d->s_h2d);
+                cudaStreamDestroy(d->s_k);
+                cudaStreamDestroy(d->s_d2h);
+                d->ready = 0;
+            }
+            if (d->d_aux) { cudaFree(d->d_aux); d->d_aux = NULL; d->aux_cap = 0; }
+            pthread_mutex_lock(&d->scratch_lock);
+            for (int i = 0; i < BC_MAX_SCRATCH; i++)
+                if (d->scratch[i].ptr) { cudaFree(d->scratch[i].ptr); memset(&d->scratch[i], 0, sizeof d->scratch[i]); }
+            pthread_mutex_unlock(&d->scratch_lock);
+        }
+        pthread_mutex_unlock(&d->lock);
+    }
+    if (prev >= 0) cudaSetDevice(prev);
+    return rc;
+}
+
 /* ------------------------------------------------------------ multi-GPU */
 
 typedef struct {

@@ -109,3 +109,17 @@ def test_rc4_long_keys_and_zero_lengths(pkg, orc):
     assert L.bc_aes_ctr_host(rk.ctypes.data, 10, bytes(16), 128, 0, None, None, 0, None) == 0
     assert L.bc_arc4_batch_host(0, None, 16, 4096, None, None, None, None) == 0
     assert L.bc_arc4_batch_host(4, None, 16, 16, None, None, None, None) == pkg.BC_ERR_BAD_ARG
+
+
+def test_shutdown_and_reuse(pkg, orc):
+    """bc_shutdown releases the library's device resources; the next call simply sets up again."""
+    rng = np.random.default_rng(15)
+    key = rng.integers(0, 256, 16, dtype=np.uint8).tobytes()
+    rke, nr = G.sched(pkg, key, ENC)
+    data = rng.integers(0, 256, 5 << 20, dtype=np.uint8)
+    want = orc.aes_ecb(key, ENC, data)
+    for _ in range(2):
+        assert np.array_equal(pkg.aes_ecb_host(rke, nr, ENC, data), want)
+        free0 = torch.cuda.mem_get_info()[0]
+        assert pkg.lib().bc_shutdown() == 0
+        assert torch.cuda.mem_get_info()[0] >= free0 + (100 << 20)       # the 3 x 64 MiB pipeline buffers came back
