@@ -204,6 +204,34 @@ def run_reference(args):
 
 # ------------------------------------------------------------------------ our arm
 
+def link_probe(d_a, d_b):
+    """What the host link allows for an in+out transfer: 1 GiB H2D and 1 GiB D2H at the same time
+    (pinned memory, monolithic copies), GB/s per direction.  The e2e figure cannot exceed it."""
+    import torch
+
+    n = min(GIB, d_a.numel())
+    h_a = torch.empty(n, dtype=torch.uint8, pin_memory=True)
+    h_b = torch.empty(n, dtype=torch.uint8, pin_memory=True)
+    s1, s2 = torch.cuda.Stream(), torch.cuda.Stream()
+    best = 1e9
+    for _ in range(3):
+        torch.cuda.synchronize()
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record()
+        s1.wait_event(e0)
+        s2.wait_event(e0)
+        with torch.cuda.stream(s1):
+            d_a[:n].copy_(h_a, non_blocking=True)
+        with torch.cuda.stream(s2):
+            h_b.copy_(d_b[:n], non_blocking=True)
+        torch.cuda.current_stream().wait_stream(s1)
+        torch.cuda.current_stream().wait_stream(s2)
+        e1.record()
+        torch.cuda.synchronize()
+        best = min(best, e0.elapsed_time(e1))
+    return n / best / 1e6
+
+
 def other_workloads(pkg, L, d_in, d_out, st, hbm_peak):
     """BASELINE configs 3 and 4 (and the metric's "batched RC4 GB/s"), device resident on 4 GiB:
     best-of-5 CUDA-event time per launch, GB/s of plaintext and the HBM fraction at the
@@ -432,6 +460,14 @@ def run_ours(args):
     }
     if others is not None:
         line["other_workloads"] = others
+    if n_gpus == 1 and not in_place:
+        try:
+            link = link_probe(d_in, d_out)
+            line["e2e"]["link_gbs_each_direction"] = round(link, 2)
+            line["e2e"]["frac_of_link"] = round(e2e_value / link, 4)
+            line["e2e"]["note"] = "host buffers in and out: bound by the PCIe link (H2D and D2H at once), not by the kernel"
+        except Exception as e:  # noqa: BLE001
+            line["e2e"]["note"] = f"link probe failed: {e}"
     if n_gpus == 1 and not args.no_cpu_baseline:
         threads = cpu_threads()
         r = ReferenceCtr(2 * GIB, threads)
