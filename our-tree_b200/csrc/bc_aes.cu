@@ -659,33 +659,23 @@ void load_sched(AesSched &ks, const uint32_t *rk, int nr)
     for (int i = 0; i < 60; i++) ks.rk[i] = (i < 4 * (nr + 1)) ? rk[i] : 0u;
 }
 
-template <typename K>
-int set_smem(K kernel, int bytes)
-{
-    BC_CUDA(cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, bytes),
-            "cudaFuncSetAttribute(MaxDynamicSharedMemorySize)");
-    return BC_OK;
-}
-
-int grid_for(uint64_t warp_items)
+/* One CTA per work item until every SM has one: small buffers spread over the
+ * SMs instead of queueing on a few (items are dealt to CTAs round-robin). */
+int grid_for(uint64_t items)
 {
     int sms = bc_cached_sm_count();
     if (sms <= 0) return -1;
-    uint64_t ctas = (warp_items + kWarps - 1) / kWarps;
-    if (ctas < 1) ctas = 1;
-    return (int)(ctas < (uint64_t)sms ? ctas : (uint64_t)sms);
+    if (items < 1) items = 1;
+    return (int)(items < (uint64_t)sms ? items : (uint64_t)sms);
 }
 
 template <int NR, int THREADS>
 int launch_ctr_t(const AesSched &ks, const CtrArgs &a, cudaStream_t st)
 {
-    int rc = set_smem(aes_ctr_kernel<NR, THREADS>, kEncSmemBytes);
+    int rc = set_smem<aes_ctr_kernel<NR, THREADS>>(kEncSmemBytes);
     if (rc) return rc;
-    const int sms = bc_cached_sm_count();
-    if (sms <= 0) return BC_ERR_CUDA;
-    uint64_t ctas = (a.n_chunks + THREADS / 32 - 1) / (THREADS / 32);
-    if (ctas < 1) ctas = 1;
-    const int grid = (int)(ctas < (uint64_t)sms ? ctas : (uint64_t)sms);
+    const int grid = grid_for(a.n_chunks);
+    if (grid < 0) return BC_ERR_CUDA;
     aes_ctr_kernel<NR, THREADS><<<grid, THREADS, kEncSmemBytes, st>>>(ks, a);
     BC_CUDA(cudaGetLastError(), "aes_ctr_kernel launch");
     return BC_OK;
@@ -701,7 +691,7 @@ template <int NR, int MODE>
 int launch_blocks(const AesSched &ks, const BlkArgs &a, cudaStream_t st)
 {
     constexpr int smem = (MODE == MODE_ECB_ENC || MODE == MODE_CFB_DEC) ? kEncSmemBytes : kDecSmemBytes;
-    int rc = set_smem(aes_blocks_kernel<NR, MODE>, smem);
+    int rc = set_smem<aes_blocks_kernel<NR, MODE>>(smem);
     if (rc) return rc;
     int grid = grid_for(a.n_groups);
     if (grid < 0) return BC_ERR_CUDA;
@@ -739,12 +729,12 @@ int launch_cbc_enc(const AesSched &ks, const CbcEncArgs &a, cudaStream_t st)
         int rc = make_row_tensor_map(&tin, a.in, a.n_msgs, msg_len);
         if (rc) return rc;
         if ((rc = make_row_tensor_map(&tout, a.out, a.n_msgs, msg_len))) return rc;
-        if ((rc = set_smem(aes_cbc_enc_batch_tma_kernel<NR, CFB>, kEncSmemBytes + kCbcTmaMaxWarps * kCbcWarpSmem))) return rc;
+        if ((rc = set_smem<aes_cbc_enc_batch_tma_kernel<NR, CFB>>(kEncSmemBytes + kCbcTmaMaxWarps * kCbcWarpSmem))) return rc;
         aes_cbc_enc_batch_tma_kernel<NR, CFB><<<grid, (int)warps * 32, smem, st>>>(ks, a, tin, tout);
         BC_CUDA(cudaGetLastError(), "aes_cbc_enc_batch_tma_kernel launch");
         return BC_OK;
     }
-    int rc = set_smem(aes_cbc_enc_batch_kernel<NR, CFB>, kEncSmemBytes);
+    int rc = set_smem<aes_cbc_enc_batch_kernel<NR, CFB>>(kEncSmemBytes);
     if (rc) return rc;
     /* spread the messages evenly: ceil(n/SMs) threads per CTA, whole warps, <= kThreads */
     uint64_t per = (a.n_msgs + sms - 1) / sms;

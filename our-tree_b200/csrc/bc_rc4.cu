@@ -384,8 +384,8 @@ rc4_batch_tma_kernel(const __grid_constant__ Rc4TmaArgs a, const __grid_constant
 template <bool KEY16>
 int launch_rc4_tma(const Rc4TmaArgs &a, const CUtensorMap &tin, const CUtensorMap &tout, cudaStream_t st)
 {
-    BC_CUDA(cudaFuncSetAttribute(rc4_batch_tma_kernel<KEY16>, cudaFuncAttributeMaxDynamicSharedMemorySize, kTmaSmem),
-            "cudaFuncSetAttribute(rc4 tma smem)");
+    int rc = set_smem<rc4_batch_tma_kernel<KEY16>>(kTmaSmem);
+    if (rc) return rc;
     const int sms = bc_cached_sm_count();
     if (sms <= 0) return BC_ERR_CUDA;
     const uint64_t groups = (a.n_streams + 31) / 32;
@@ -411,8 +411,8 @@ __global__ void xor_kernel(const uint4 *a, const uint4 *b, uint4 *o, uint64_t n1
 template <bool VEC, bool KEY16>
 int launch_rc4(const Rc4Args &a, cudaStream_t st)
 {
-    BC_CUDA(cudaFuncSetAttribute(rc4_batch_kernel<VEC, KEY16>, cudaFuncAttributeMaxDynamicSharedMemorySize, kRc4Smem),
-            "cudaFuncSetAttribute(rc4 smem)");
+    int rc = set_smem<rc4_batch_kernel<VEC, KEY16>>(kRc4Smem);
+    if (rc) return rc;
     const int sms = bc_cached_sm_count();
     if (sms <= 0) return BC_ERR_CUDA;
     uint64_t ctas = (a.n_streams + kRc4Threads - 1) / kRc4Threads;

@@ -19,6 +19,21 @@
 
 namespace {
 
+/* Raise the kernel's dynamic shared-memory limit, once per device and kernel
+ * (cudaFuncSetAttribute costs microseconds, which matters for small buffers). */
+template <auto Kernel>
+int set_smem(int bytes)
+{
+    static int done_bytes[64];
+    int dev = 0;
+    BC_CUDA(cudaGetDevice(&dev), "cudaGetDevice");
+    if (dev >= 0 && dev < 64 && __atomic_load_n(&done_bytes[dev], __ATOMIC_ACQUIRE) >= bytes) return BC_OK;
+    BC_CUDA(cudaFuncSetAttribute(Kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, bytes),
+            "cudaFuncSetAttribute(MaxDynamicSharedMemorySize)");
+    if (dev >= 0 && dev < 64) __atomic_store_n(&done_bytes[dev], bytes, __ATOMIC_RELEASE);
+    return BC_OK;
+}
+
 constexpr int kSlab     = 64;            /* bytes of one row per box */
 constexpr int kBoxBytes = 32 * kSlab;    /* 2 KB per box */
 
