@@ -172,6 +172,39 @@ class ReferenceCtr:
         return self.nbytes / float(np.median([self.one_pass() for _ in range(passes)])) / 1e9
 
 
+def reference_extras(threads: int):
+    """The reference's other CPU paths on the same host cores, bounded samples: aes.c's table-driven
+    aes_crypt_ctr (the path the kernels restate) and arc4.c over independent 4 KiB streams
+    (setup + prep + crypt each, BASELINE config 4's shape).  GB/s over all `threads` cores."""
+    from concurrent.futures import ThreadPoolExecutor
+
+    import oracle
+
+    use_ref = oracle.Ref.available()
+    impl = oracle.Ref() if use_ref else oracle.Oracle()
+    tag = "oracle/_ref/libref.so" if use_ref else "oracle.c port"
+    rng = np.random.default_rng(99)
+    per = 8 << 20                                               # 8 MiB per thread per pass
+    buf = np.frombuffer(rng.bytes(per), dtype=np.uint8)
+    keys = np.frombuffer(rng.bytes((per // 4096) * 16), dtype=np.uint8)
+    out = {}
+    with ThreadPoolExecutor(threads) as ex:
+        def ctr(_):
+            impl.aes_ctr(KEY, COUNTER, buf)
+        def rc4(_):
+            impl.arc4_batch(keys, 16, buf, 4096)
+        for name, fn, what in (("aes_c_ctr", ctr, "aes.c aes_crypt_ctr"), ("arc4_c_batched_4k", rc4, "arc4.c setup+prep+crypt per 4 KiB stream")):
+            list(ex.map(fn, range(threads)))
+            ts = []
+            for _ in range(3):
+                t0 = time.perf_counter()
+                list(ex.map(fn, range(threads)))
+                ts.append(time.perf_counter() - t0)
+            out[name] = {"value": round(per * threads / float(np.median(ts)) / 1e9, 3), "unit": UNIT, "cores": threads,
+                         "sample": f"{what} ({tag}, gcc -O2); {per >> 20} MiB per thread x {threads} threads, median of 3"}
+    return out
+
+
 def run_reference(args):
     rank = int(os.environ.get("RANK", "0"))
     if rank != 0:
@@ -475,6 +508,10 @@ def run_ours(args):
         line["cpu_baseline"] = {"value": round(gbs, 3), "unit": UNIT, "cores": threads, "kind": r.kind,
                                 "sample": f"{r.what}; {r.nbytes >> 20} MiB split over {threads} threads, "
                                           "median of 7 passes"}
+        try:
+            line["cpu_baseline"]["other_reference_paths"] = reference_extras(threads)
+        except Exception as e:  # noqa: BLE001
+            line["cpu_baseline"]["other_reference_paths"] = {"error": str(e)}
     print(json.dumps(line), flush=True)
     if distributed:
         dist.destroy_process_group()
