@@ -53,17 +53,22 @@ __device__ __forceinline__ void mbar_expect_tx(uint32_t bar, uint32_t bytes)
     asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" :: "r"(bar), "r"(bytes) : "memory");
 }
 
+/* Wait for the phase with the given parity.  try_wait suspends the thread for a hardware time
+ * slice per attempt; a box that never arrives (a bad tensor map, say) traps after a few seconds
+ * instead of hanging the GPU. */
 __device__ __forceinline__ void mbar_wait(uint32_t bar, uint32_t parity)
 {
-    asm volatile(
-        "{\n"
-        ".reg .pred p;\n"
-        "WAIT_LOOP:\n"
-        "mbarrier.try_wait.parity.shared::cta.b64 p, [%0], %1;\n"
-        "@p bra WAIT_DONE;\n"
-        "bra WAIT_LOOP;\n"
-        "WAIT_DONE:\n"
-        "}\n" :: "r"(bar), "r"(parity) : "memory");
+    for (uint32_t spins = 0;; spins++) {
+        uint32_t done;
+        asm volatile(
+            "{\n"
+            ".reg .pred p;\n"
+            "mbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2;\n"
+            "selp.u32 %0, 1, 0, p;\n"
+            "}\n" : "=r"(done) : "r"(bar), "r"(parity) : "memory");
+        if (done) return;
+        if (spins > (1u << 24)) asm volatile("trap;");
+    }
 }
 
 __device__ __forceinline__ void tma_load_2d(uint32_t dst, const CUtensorMap *tm, uint32_t c0, uint32_t c1, uint32_t bar)
