@@ -123,3 +123,51 @@ def test_shutdown_and_reuse(pkg, orc):
         free0 = torch.cuda.mem_get_info()[0]
         assert pkg.lib().bc_shutdown() == 0
         assert torch.cuda.mem_get_info()[0] >= free0 + (100 << 20)       # the 3 x 64 MiB pipeline buffers came back
+
+
+def test_resumable_calls_random_splits(pkg, orc):
+    """The reference's resumable state (nc_off / nonce_counter / stream_block, iv_off / iv, arc4 x / y / m,
+    rc4 index1 / index2 / perm) under random call splits: every split must give the same bytes and the
+    same final state as the oracle fed the same splits."""
+    rng = np.random.default_rng(2718)
+    for trial in range(12):
+        kb = (128, 192, 256)[trial % 3]
+        key = rng.integers(0, 256, kb // 8, dtype=np.uint8).tobytes()
+        rc, e = pkg.aes_setkey_enc(key)
+        total = int(rng.integers(1, 5000))
+        data = rng.integers(0, 256, total, dtype=np.uint8).tobytes()
+        cuts = sorted(set(int(c) for c in rng.integers(0, total + 1, int(rng.integers(0, 6)))))
+        parts = [data[a:b] for a, b in zip([0] + cuts, cuts + [total])]
+        nc0 = bytes(rng.integers(0, 256, 16 - trial % 5, dtype=np.uint8)) + b"\xff" * (trial % 5)
+        iv0 = rng.integers(0, 256, 16, dtype=np.uint8).tobytes()
+        # CTR
+        nc, sb, off, got = nc0, bytes(16), 0, []
+        onc, osb, ooff, want = nc0, bytes(16), 0, []
+        for p in parts:
+            rc, o, off, nc, sb = pkg.aes_crypt_ctr(e, nc, p, off, sb)
+            assert rc == 0
+            got.append(o.tobytes())
+            o2, ooff, onc, osb = orc.aes_ctr(key, onc, p, ooff, osb)
+            want.append(o2.tobytes())
+        assert b"".join(got) == b"".join(want) and (off, nc, sb) == (ooff, onc, osb)
+        # CFB128, both directions
+        for mode in (1, 0):
+            iv, off, got = iv0, 0, []
+            oiv, ooff, want = iv0, 0, []
+            for p in parts:
+                rc, o, off, iv = pkg.aes_crypt_cfb128(e, mode, iv, p, off)
+                assert rc == 0
+                got.append(o.tobytes())
+                o2, ooff, oiv = orc.aes_cfb128(key, mode, oiv, p, ooff)
+                want.append(o2.tobytes())
+            assert b"".join(got) == b"".join(want) and (off, iv) == (ooff, oiv)
+        # ARC4 keystream chaining and rc4_crypt chaining
+        rkey = rng.integers(0, 256, int(rng.integers(1, 40)), dtype=np.uint8).tobytes()
+        c = pkg.arc4_setup(rkey)
+        ks = np.concatenate([pkg.arc4_prep(c, len(p)) for p in parts] + [np.zeros(0, np.uint8)])
+        wks, x, y, m = orc.arc4_keystream(rkey, [len(p) for p in parts])
+        assert np.array_equal(ks, wks) and (c.x, c.y, bytes(c.m)) == (x, y, m)
+        st = pkg.rc4_init(rkey)
+        out = np.concatenate([pkg.rc4_crypt(st, p) for p in parts] + [np.zeros(0, np.uint8)])
+        wout, i1, i2, perm = orc.rc4(rkey, parts)
+        assert np.array_equal(out, wout) and (st.index1, st.index2, bytes(st.perm)) == (i1, i2, perm)
