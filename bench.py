@@ -315,6 +315,22 @@ def other_workloads(pkg, L, d_in, d_out, st, hbm_peak):
         ms = best_ms(fn)
         out[name] = {"value": round(n / ms / 1e6, 1), "unit": UNIT, "kernel_ms": round(ms, 4),
                      "hbm_frac": round(traffic / ms / 1e6 / hbm_peak, 4)}
+    # batched RC4 end to end: pinned host buffers through bc_arc4_batch_host (1 GiB = 2^18 streams x 4 KiB)
+    hn = GIB
+    h_in, h_out, h_keys = L.bc_host_alloc(hn), L.bc_host_alloc(hn), L.bc_host_alloc((hn // 4096) * 16)
+    if h_in and h_out and h_keys:
+        np.ctypeslib.as_array((ctypes.c_ubyte * hn).from_address(h_in))[:] = 0x5A
+        np.ctypeslib.as_array((ctypes.c_ubyte * ((hn // 4096) * 16)).from_address(h_keys))[:] = np.resize(
+            np.frombuffer(np.random.default_rng(5).bytes(1 << 20), dtype=np.uint8), (hn // 4096) * 16)
+        ts = []
+        for _ in range(4):
+            t0 = time.perf_counter()
+            pkg.check(L.bc_arc4_batch_host(hn // 4096, h_keys, 16, 4096, h_in, h_out, None, None))
+            ts.append(time.perf_counter() - t0)
+        out["rc4_batched_host_buffers_1gib"] = {"value": round(hn / min(ts[1:]) / 1e9, 2), "unit": UNIT,
+                                                 "api": "bc_arc4_batch_host (pinned buffers, H2D + kernel + D2H)"}
+    for p in (h_in, h_out, h_keys):
+        L.bc_host_free(p)
     return out
 
 

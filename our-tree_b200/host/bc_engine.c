@@ -633,18 +633,43 @@ int bc_aes_cfb128_decrypt_host(const uint32_t *rk, int nr, const unsigned char i
     return chained_decrypt_host(1, rk, nr, iv, in, out, nbytes);
 }
 
+/* Small per-item side data of the batched calls (IVs, keys): moved to / from the device in ONE
+ * copy around the pipeline.  Copying it chunk by chunk would queue each small copy behind the
+ * data copies already enqueued for later chunks on the same DMA engine and stall the kernels. */
+static int side_upload(bc_dev *d, void *key, const void *host, size_t bytes, void **dev)
+{
+    int rc = bc_scratch_get(key, bytes, dev);
+    if (rc) return rc;
+    BC_CUDA(cudaMemcpyAsync(*dev, host, bytes, cudaMemcpyHostToDevice, d->s_k), "cudaMemcpyAsync side data");
+    BC_CUDA(cudaStreamSynchronize(d->s_k), "cudaStreamSynchronize");
+    return BC_OK;
+}
+
+static int side_download(bc_dev *d, void *host, const void *dev, size_t bytes)
+{
+    BC_CUDA(cudaMemcpyAsync(host, dev, bytes, cudaMemcpyDeviceToHost, d->s_k), "cudaMemcpyAsync side data");
+    BC_CUDA(cudaStreamSynchronize(d->s_k), "cudaStreamSynchronize");
+    return BC_OK;
+}
+
 /* ------------------------------------------- AES-CBC encrypt, batched msgs */
 
 typedef struct {
     const uint32_t *rk; int nr; size_t msg_len; size_t msgs_per_chunk;
     const unsigned char *ivs; unsigned char *ivs_out; unsigned char *d_ivs;   /* [BC_SLOTS][msgs_per_chunk][16] */
     size_t n_msgs; int cfb;
+    unsigned char *d_ivs_all;   /* [n_msgs][16] resident for the whole call (in and out), or NULL */
 } cbce_op;
 
 static int cbce_chunk(void *arg, size_t idx, size_t off, size_t n, void *d, cudaStream_t st)
 {
     cbce_op *o = (cbce_op *)arg;
     const size_t m0 = off / o->msg_len, nm = n / o->msg_len;
+    if (o->d_ivs_all) {
+        unsigned char *v = o->d_ivs_all + 16 * m0;
+        return (o->cfb ? bc_aes_cfb128_encrypt_batch_dev : bc_aes_cbc_encrypt_batch_dev)(
+            o->rk, o->nr, nm, o->msg_len, v, o->ivs_out ? v : NULL, d, d, st);
+    }
     unsigned char *d_iv = o->d_ivs + (idx % BC_SLOTS) * o->msgs_per_chunk * 16;
     BC_CUDA(cudaMemcpyAsync(d_iv, o->ivs + 16 * m0, 16 * nm, cudaMemcpyHostToDevice, st), "cudaMemcpyAsync ivs");
     int rc = (o->cfb ? bc_aes_cfb128_encrypt_batch_dev : bc_aes_cbc_encrypt_batch_dev)(
@@ -673,11 +698,13 @@ static int chained_encrypt_batch_host(int cfb, const uint32_t *rk, int nr, size_
     if ((rc = dev_ensure_slots(d)) == BC_OK) {
         if (msg_len <= BC_CHUNK_BYTES) {
             cbce_op o = { rk, nr, msg_len, BC_CHUNK_BYTES / msg_len, (const unsigned char *)ivs,
-                          (unsigned char *)ivs_out, NULL, n_msgs, cfb };
-            if ((rc = dev_ensure_aux(d, BC_SLOTS * o.msgs_per_chunk * 16)) == BC_OK) {
-                o.d_ivs = d->d_aux;
+                          (unsigned char *)ivs_out, NULL, n_msgs, cfb, NULL };
+            void *all = NULL;
+            if ((rc = side_upload(d, (void *)&d->aux_cap, ivs, 16 * n_msgs, &all)) == BC_OK) {
+                o.d_ivs_all = (unsigned char *)all;
                 rc = run_pipeline(d, (const unsigned char *)in, (unsigned char *)out, n_msgs * msg_len,
                                   o.msgs_per_chunk * msg_len, cbce_chunk, &o);
+                if (rc == BC_OK && ivs_out) rc = side_download(d, ivs_out, all, 16 * n_msgs);
             }
         } else {
             /* a message longer than one pipeline buffer: walk it in pieces, the chain value
@@ -687,7 +714,7 @@ static int chained_encrypt_batch_host(int cfb, const uint32_t *rk, int nr, size_
                 memcpy(iv, (const unsigned char *)ivs + 16 * m, 16);
                 for (size_t off = 0; off < msg_len && rc == BC_OK; off += BC_CHUNK_BYTES) {
                     size_t n = msg_len - off < BC_CHUNK_BYTES ? msg_len - off : BC_CHUNK_BYTES;
-                    cbce_op o = { rk, nr, n, 1, iv, iv, NULL, 1, cfb };
+                    cbce_op o = { rk, nr, n, 1, iv, iv, NULL, 1, cfb, NULL };
                     if ((rc = dev_ensure_aux(d, BC_SLOTS * 16)) != BC_OK) break;
                     o.d_ivs = d->d_aux;
                     rc = run_pipeline(d, (const unsigned char *)in + m * msg_len + off,
@@ -724,6 +751,7 @@ typedef struct {
     const unsigned char *keys; const unsigned char *ctx_in; unsigned char *ctx_out;
     unsigned char *d_keys;      /* [BC_SLOTS][streams_per_chunk][keylen] */
     unsigned char *d_ctx;       /* [BC_SLOTS][streams_per_chunk][264] when contexts travel */
+    unsigned char *d_keys_all;  /* [n_streams][keylen] resident for the whole call, or NULL */
 } rc4_op;
 
 /* streams [s0, s0+ns) of the call, data (if any) already in `d` */
@@ -734,6 +762,8 @@ static int rc4_issue(rc4_op *o, size_t slot, size_t s0, size_t ns, void *d, cuda
     if (o->ctx_in)
         BC_CUDA(cudaMemcpyAsync(d_ctx, o->ctx_in + s0 * BC_ARC4_CTX_BYTES, ns * BC_ARC4_CTX_BYTES,
                                 cudaMemcpyHostToDevice, st), "cudaMemcpyAsync ctx_in");
+    else if (o->d_keys_all)
+        d_keys = o->d_keys_all + s0 * o->keylen;
     else
         BC_CUDA(cudaMemcpyAsync(d_keys, o->keys + s0 * o->keylen, ns * o->keylen, cudaMemcpyHostToDevice, st),
                 "cudaMemcpyAsync keys");
@@ -774,7 +804,12 @@ int bc_arc4_batch_host(size_t n_streams, const void *keys, unsigned keylen, size
             size_t spc = length ? BC_CHUNK_BYTES / length : 4096;
             if (spc > 65536) spc = 65536;
             rc4_op o = { length, keylen, spc, in == NULL, (const unsigned char *)keys, (const unsigned char *)ctx_in,
-                         (unsigned char *)ctx_out, NULL, NULL };
+                         (unsigned char *)ctx_out, NULL, NULL, NULL };
+            if (!ctx_in) {
+                void *all = NULL;
+                if ((rc = side_upload(d, (void *)&d->aux_cap, keys, n_streams * keylen, &all)) != BC_OK) goto rc4_done;
+                o.d_keys_all = (unsigned char *)all;
+            }
             size_t need_keys = (BC_SLOTS * spc * keylen + 255) & ~(size_t)255;
             size_t need_ctx = with_ctx ? BC_SLOTS * spc * BC_ARC4_CTX_BYTES : 0;
             if ((rc = dev_ensure_aux(d, need_keys + need_ctx)) == BC_OK) {
@@ -805,7 +840,7 @@ int bc_arc4_batch_host(size_t n_streams, const void *keys, unsigned keylen, size
                 for (size_t off = 0; off < length && rc == BC_OK; off += BC_CHUNK_BYTES) {
                     size_t n = length - off < BC_CHUNK_BYTES ? length - off : BC_CHUNK_BYTES;
                     rc4_op o = { n, keylen, 1, in == NULL, keys ? (const unsigned char *)keys + s * keylen : NULL,
-                                 have_ctx ? ctx : NULL, ctx, NULL, NULL };
+                                 have_ctx ? ctx : NULL, ctx, NULL, NULL, NULL };
                     size_t need_keys = (BC_SLOTS * (size_t)keylen + 255) & ~(size_t)255;
                     if ((rc = dev_ensure_aux(d, need_keys + BC_SLOTS * BC_ARC4_CTX_BYTES)) != BC_OK) break;
                     o.d_keys = d->d_aux;
@@ -818,6 +853,7 @@ int bc_arc4_batch_host(size_t n_streams, const void *keys, unsigned keylen, size
             }
         }
     }
+rc4_done:
     pthread_mutex_unlock(&d->lock);
     return rc;
 }
