@@ -860,18 +860,25 @@ rc4_done:
 
 /* out = a ^ b on host buffers (arc4_crypt, arc4.c:101-112).  `a` rides the pipeline
  * buffer, `b` a second device buffer per slot. */
-typedef struct { const unsigned char *b; unsigned char *d_b; int b_pinned; } xor_op;
+typedef struct { const unsigned char *b; unsigned char *d_b; bc_dev *dev; } xor_op;
 
 static int xor_chunk(void *arg, size_t idx, size_t off, size_t n, void *d, cudaStream_t st)
 {
     xor_op *o = (xor_op *)arg;
-    unsigned char *d_b = o->d_b + (idx % BC_SLOTS) * BC_CHUNK_BYTES;
-    /* Same stream as the kernel, pinned or not: for pageable memory the runtime stages the copy
-     * and keeps it ordered inside `st`.  (A plain cudaMemcpy would run on the legacy stream, which
-     * the non-blocking pipeline streams do not wait for — its last staged piece could still be in
-     * flight when the XOR kernel starts.) */
-    (void)o->b_pinned;
-    BC_CUDA(cudaMemcpyAsync(d_b, o->b + off, n, cudaMemcpyHostToDevice, st), "cudaMemcpyAsync b");
+    const int sl = (int)(idx % BC_SLOTS);
+    unsigned char *d_b = o->d_b + (size_t)sl * BC_CHUNK_BYTES;
+    if (st == o->dev->s_k) {
+        /* enqueue-ahead pipeline: the second operand rides the H2D stream right behind the first
+         * (on the kernel stream it would queue behind the next chunks' copies), an event orders it */
+        BC_CUDA(cudaMemcpyAsync(d_b, o->b + off, n, cudaMemcpyHostToDevice, o->dev->s_h2d), "cudaMemcpyAsync b");
+        BC_CUDA(cudaEventRecord(o->dev->e_h2d[sl], o->dev->s_h2d), "cudaEventRecord");
+        BC_CUDA(cudaStreamWaitEvent(st, o->dev->e_h2d[sl], 0), "cudaStreamWaitEvent");
+    } else {
+        /* host-in-the-loop pipeline: same stream as the kernel; for pageable memory the runtime
+         * stages the copy and keeps it ordered inside `st`.  (A plain cudaMemcpy would run on the
+         * legacy stream, which the non-blocking pipeline streams do not wait for.) */
+        BC_CUDA(cudaMemcpyAsync(d_b, o->b + off, n, cudaMemcpyHostToDevice, st), "cudaMemcpyAsync b");
+    }
     return bc_xor_dev(d, d_b, d, n, st);
 }
 
@@ -886,7 +893,7 @@ int bc_xor_host(const void *a, const void *b, void *out, size_t nbytes)
     if ((rc = dev_ensure_slots(d)) == BC_OK) {
         void *d_b = NULL;
         if ((rc = bc_scratch_get((void *)d, BC_SLOTS * BC_CHUNK_BYTES, &d_b)) == BC_OK) {
-            xor_op o = { (const unsigned char *)b, (unsigned char *)d_b, classify(b) == 1 };
+            xor_op o = { (const unsigned char *)b, (unsigned char *)d_b, d };
             rc = run_pipeline(d, (const unsigned char *)a, (unsigned char *)out, nbytes, BC_CHUNK_BYTES, xor_chunk, &o);
         }
     }
