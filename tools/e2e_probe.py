@@ -27,11 +27,16 @@ def main():
         np.ctypeslib.as_array((ctypes.c_ubyte * n).from_address(h_in))[:] = 7
     nc = bytes(16)
     ts = []
+    zerocopy = len(sys.argv) > 2 and sys.argv[2] == "zerocopy"
     for _ in range(4):
         t0 = time.perf_counter()
-        pkg.check(L.bc_aes_ctr_host(rk.ctypes.data, 10, nc, 128, 0, h_in, h_out, n, None))
+        if zerocopy:      # the kernel reads / writes the pinned host buffers itself over PCIe (UVA), no staging
+            pkg.check(L.bc_aes_ctr_dev(rk.ctypes.data, 10, nc, 128, 0, h_in, h_out, n, None, None))
+            pkg.check(L.bc_device_sync())
+        else:
+            pkg.check(L.bc_aes_ctr_host(rk.ctypes.data, 10, nc, 128, 0, h_in, h_out, n, None))
         ts.append(time.perf_counter() - t0)
-    print(("pageable " if pageable else "pinned ") + f"copy_threads={os.environ.get('BULKCIPHER_COPY_THREADS', 'auto')} " + f"chunk={os.environ.get('BULKCIPHER_CHUNK_MIB', '32')}MiB slots={os.environ.get('BULKCIPHER_SLOTS', '3')} "
+    print(("zerocopy " if zerocopy else "") + ("pageable " if pageable else "pinned ") + f"copy_threads={os.environ.get('BULKCIPHER_COPY_THREADS', 'auto')} " + f"chunk={os.environ.get('BULKCIPHER_CHUNK_MIB', '32')}MiB slots={os.environ.get('BULKCIPHER_SLOTS', '3')} "
           f"best {n / min(ts[1:]) / 1e9:.2f} GB/s  median {n / float(np.median(ts[1:])) / 1e9:.2f} GB/s")
 
 
