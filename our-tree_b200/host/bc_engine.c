@@ -319,6 +319,9 @@ static void par_memcpy(void *dst, const void *src, size_t n)
     pthread_mutex_unlock(&g_copy_user);
 }
 
+/* test hook (tests/c/host_san_test.c): the staging copy without a device */
+void bc_internal_par_memcpy(void *dst, const void *src, size_t n) { par_memcpy(dst, src, n); }
+
 /* ------------------------------------------------------- pipeline plumbing */
 
 static int dev_prepare(bc_dev **out)

@@ -114,3 +114,20 @@ def test_product_does_not_reference_oracle():
                 text = open(os.path.join(dirpath, f), errors="replace").read()
                 assert "liboracle" not in text and "orc_" not in text and "libref" not in text, f
                 assert not re.search(r"^\s*(import|from)\s+oracle", text, flags=re.M), f
+
+
+def test_host_layer_under_sanitizers():
+    """host/*.c under AddressSanitizer + UBSan with stubbed launchers (tests/c/host_san_test.c): key
+    schedules vs FIPS-197 A.1/A.3, error codes, "no device => fail, never emulate", the staging copy pool."""
+    import shutil
+    import subprocess
+    if not os.path.exists("/usr/bin/gcc") and not shutil.which("gcc"):
+        pytest.skip("no gcc")
+    pkgdir = os.path.join(ROOT, "our-tree_b200")
+    b = subprocess.run(["make", "-C", pkgdir, "host-san-test"], capture_output=True, text=True)
+    if b.returncode != 0 and ("-lasan" in b.stderr or "libasan" in b.stderr):
+        pytest.skip("sanitizer runtime not installed")
+    assert b.returncode == 0, b.stdout + b.stderr
+    env = dict(os.environ, ASAN_OPTIONS="detect_leaks=0", UBSAN_OPTIONS="halt_on_error=1")
+    r = subprocess.run([os.path.join(pkgdir, "build", "host_san_test")], capture_output=True, text=True, env=env, timeout=300)
+    assert r.returncode == 0 and "host_san_test: ok" in r.stdout, r.stdout + r.stderr
