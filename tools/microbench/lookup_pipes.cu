@@ -53,6 +53,28 @@ __global__ void __launch_bounds__(THREADS, 1) k(cudaTextureObject_t tex, const u
     if (threadIdx.x == 0) cycles[blockIdx.x] = t1 - t0;
 }
 
+// LOP3 issue rate: 8 independent chains of 3-input logic ops per thread (what a bitsliced AES is made of)
+__global__ void __launch_bounds__(THREADS, 1) k_lop3(uint32_t *out, long long *cycles, uint32_t seed)
+{
+    uint32_t r[8];
+    for (int i = 0; i < 8; i++) r[i] = threadIdx.x * 2654435761u + seed * (i + 1);
+    long long t0 = clock64();
+#pragma unroll 1
+    for (int it = 0; it < ITERS; it++) {
+#pragma unroll
+        for (int u = 0; u < 16; u++) {
+#pragma unroll
+            for (int i = 0; i < 8; i++)
+                asm volatile("lop3.b32 %0, %0, %1, %2, 0x96;" : "+r"(r[i]) : "r"(r[(i + 3) & 7]), "r"(r[(i + 5) & 7]));
+        }
+    }
+    long long t1 = clock64();
+    uint32_t x = 0;
+    for (int i = 0; i < 8; i++) x ^= r[i];
+    out[blockIdx.x * THREADS + threadIdx.x] = x;
+    if (threadIdx.x == 0) cycles[blockIdx.x] = t1 - t0;
+}
+
 template <int MODE, int RATIO>
 int run(const char *name, cudaTextureObject_t tex, uint32_t *gtab, uint32_t *out, long long *cyc, int sms)
 {
@@ -86,6 +108,15 @@ int main()
     rd.res.linear.desc = cudaCreateChannelDesc<unsigned>(); rd.res.linear.sizeInBytes = 1024;
     cudaTextureDesc td = {}; td.readMode = cudaReadModeElementType;
     cudaTextureObject_t tex; CK(cudaCreateTextureObject(&tex, &rd, &td, nullptr));
+    k_lop3<<<sms, THREADS>>>(out, cyc, 1);
+    CK(cudaDeviceSynchronize());
+    k_lop3<<<sms, THREADS>>>(out, cyc, 2);
+    CK(cudaDeviceSynchronize());
+    {
+        long long c0; cudaMemcpy(&c0, cyc, 8, cudaMemcpyDeviceToHost);
+        double ops = 8.0 * 16 * ITERS * THREADS;
+        printf("%-34s cycles %10lld  LOP3 lane-ops/clk/SM %6.2f\n", "LOP3 only (8 chains)", c0, ops / (double)c0);
+    }
     run<0, 4>("LDS only (16/trip)", tex, gtab, out, cyc, sms);
     run<1, 1>("TEX only (4/trip)", tex, gtab, out, cyc, sms);
     run<2, 4>("LDS 16 + TEX 2", tex, gtab, out, cyc, sms);
