@@ -135,16 +135,34 @@ struct Tb { uint32_t base, lane4; };
 /* TB(OFF, K, x): table at byte offset OFF, indexed by byte K of x — one PRMT + one LDS */
 #define TB(OFF, K, x) lds32<OFF>(tb.base + baddr<K>((x), tb.lane4))
 
+/* TBL(k, K, x): forward/reverse table k (FTk / RTk) indexed by byte K of x.  Default: four
+ * tables in shared memory.  BC_SINGLE_TABLE=1 is the "__byte_perm formulation" of the north
+ * star: only table 0 is looked up and tables 1-3 are its byte rotations (aes.c:420-422), one
+ * extra PRMT per lookup — kept as an A/B knob (profiles/r1_summary.md), it loses because the
+ * ALU pipe then saturates before the shared-memory pipe. */
+#ifndef BC_SINGLE_TABLE
+#define BC_SINGLE_TABLE 0
+#endif
+template <int k> __device__ __forceinline__ uint32_t rot_table(uint32_t v)
+{
+    return k == 0 ? v : __byte_perm(v, 0, k == 1 ? 0x2103 : k == 2 ? 0x1032 : 0x0321);
+}
+#if BC_SINGLE_TABLE
+#define TBL(k, K, x) rot_table<k>(TB(OFF_T0, K, x))
+#else
+#define TBL(k, K, x) TB((k) == 0 ? OFF_T0 : (k) == 1 ? OFF_T1 : (k) == 2 ? OFF_T2 : OFF_T3, K, x)
+#endif
+
 struct State { uint32_t a, b, c, d; };
 
 /* one forward table round, AES_FROUND (aes.c:601-622) */
 __device__ __forceinline__ State enc_round(const State s, const uint32_t *rk, const Tb tb)
 {
     State t;
-    t.a = TB(OFF_T0, 0, s.a) ^ TB(OFF_T1, 1, s.b) ^ TB(OFF_T2, 2, s.c) ^ TB(OFF_T3, 3, s.d) ^ rk[0];
-    t.b = TB(OFF_T0, 0, s.b) ^ TB(OFF_T1, 1, s.c) ^ TB(OFF_T2, 2, s.d) ^ TB(OFF_T3, 3, s.a) ^ rk[1];
-    t.c = TB(OFF_T0, 0, s.c) ^ TB(OFF_T1, 1, s.d) ^ TB(OFF_T2, 2, s.a) ^ TB(OFF_T3, 3, s.b) ^ rk[2];
-    t.d = TB(OFF_T0, 0, s.d) ^ TB(OFF_T1, 1, s.a) ^ TB(OFF_T2, 2, s.b) ^ TB(OFF_T3, 3, s.c) ^ rk[3];
+    t.a = TBL(0, 0, s.a) ^ TBL(1, 1, s.b) ^ TBL(2, 2, s.c) ^ TBL(3, 3, s.d) ^ rk[0];
+    t.b = TBL(0, 0, s.b) ^ TBL(1, 1, s.c) ^ TBL(2, 2, s.d) ^ TBL(3, 3, s.a) ^ rk[1];
+    t.c = TBL(0, 0, s.c) ^ TBL(1, 1, s.d) ^ TBL(2, 2, s.a) ^ TBL(3, 3, s.b) ^ rk[2];
+    t.d = TBL(0, 0, s.d) ^ TBL(1, 1, s.a) ^ TBL(2, 2, s.b) ^ TBL(3, 3, s.c) ^ rk[3];
     return t;
 }
 
@@ -152,10 +170,10 @@ __device__ __forceinline__ State enc_round(const State s, const uint32_t *rk, co
 __device__ __forceinline__ State dec_round(const State s, const uint32_t *rk, const Tb tb)
 {
     State t;
-    t.a = TB(OFF_T0, 0, s.a) ^ TB(OFF_T1, 1, s.d) ^ TB(OFF_T2, 2, s.c) ^ TB(OFF_T3, 3, s.b) ^ rk[0];
-    t.b = TB(OFF_T0, 0, s.b) ^ TB(OFF_T1, 1, s.a) ^ TB(OFF_T2, 2, s.d) ^ TB(OFF_T3, 3, s.c) ^ rk[1];
-    t.c = TB(OFF_T0, 0, s.c) ^ TB(OFF_T1, 1, s.b) ^ TB(OFF_T2, 2, s.a) ^ TB(OFF_T3, 3, s.d) ^ rk[2];
-    t.d = TB(OFF_T0, 0, s.d) ^ TB(OFF_T1, 1, s.c) ^ TB(OFF_T2, 2, s.b) ^ TB(OFF_T3, 3, s.a) ^ rk[3];
+    t.a = TBL(0, 0, s.a) ^ TBL(1, 1, s.d) ^ TBL(2, 2, s.c) ^ TBL(3, 3, s.b) ^ rk[0];
+    t.b = TBL(0, 0, s.b) ^ TBL(1, 1, s.a) ^ TBL(2, 2, s.d) ^ TBL(3, 3, s.c) ^ rk[1];
+    t.c = TBL(0, 0, s.c) ^ TBL(1, 1, s.b) ^ TBL(2, 2, s.a) ^ TBL(3, 3, s.d) ^ rk[2];
+    t.d = TBL(0, 0, s.d) ^ TBL(1, 1, s.c) ^ TBL(2, 2, s.b) ^ TBL(3, 3, s.a) ^ rk[3];
     return t;
 }
 
@@ -170,10 +188,10 @@ __device__ __forceinline__ uint32_t merge_bytes(uint32_t w0, uint32_t w1, uint32
 __device__ __forceinline__ State enc_last(const State s, const uint32_t *rk, const Tb tb)
 {
     State t;
-    t.a = merge_bytes(TB(OFF_T2, 0, s.a), TB(OFF_T3, 1, s.b), TB(OFF_T0, 2, s.c), TB(OFF_T1, 3, s.d)) ^ rk[0];
-    t.b = merge_bytes(TB(OFF_T2, 0, s.b), TB(OFF_T3, 1, s.c), TB(OFF_T0, 2, s.d), TB(OFF_T1, 3, s.a)) ^ rk[1];
-    t.c = merge_bytes(TB(OFF_T2, 0, s.c), TB(OFF_T3, 1, s.d), TB(OFF_T0, 2, s.a), TB(OFF_T1, 3, s.b)) ^ rk[2];
-    t.d = merge_bytes(TB(OFF_T2, 0, s.d), TB(OFF_T3, 1, s.a), TB(OFF_T0, 2, s.b), TB(OFF_T1, 3, s.c)) ^ rk[3];
+    t.a = merge_bytes(TBL(2, 0, s.a), TBL(3, 1, s.b), TBL(0, 2, s.c), TBL(1, 3, s.d)) ^ rk[0];
+    t.b = merge_bytes(TBL(2, 0, s.b), TBL(3, 1, s.c), TBL(0, 2, s.d), TBL(1, 3, s.a)) ^ rk[1];
+    t.c = merge_bytes(TBL(2, 0, s.c), TBL(3, 1, s.d), TBL(0, 2, s.a), TBL(1, 3, s.b)) ^ rk[2];
+    t.d = merge_bytes(TBL(2, 0, s.d), TBL(3, 1, s.a), TBL(0, 2, s.b), TBL(1, 3, s.c)) ^ rk[3];
     return t;
 }
 
@@ -229,10 +247,10 @@ __device__ __forceinline__ State ctr_keystream(uint32_t c0, uint32_t d0, uint32_
 {
     const uint32_t x0 = c0 ^ f;
     State s;
-    s.a = d0 ^ TB(OFF_T0, 0, x0);
-    s.b = d1 ^ TB(OFF_T3, 3, x0);
-    s.c = d2 ^ TB(OFF_T2, 2, x0);
-    s.d = d3 ^ TB(OFF_T1, 1, x0);
+    s.a = d0 ^ TBL(0, 0, x0);
+    s.b = d1 ^ TBL(3, 3, x0);
+    s.c = d2 ^ TBL(2, 2, x0);
+    s.d = d3 ^ TBL(1, 1, x0);
 #pragma unroll
     for (int r = 3; r < NR; r++) s = enc_round(s, ks.rk + 4 * r, tb);
     return enc_last(s, ks.rk + 4 * NR, tb);
@@ -300,14 +318,14 @@ aes_ctr_kernel(const __grid_constant__ AesSched ks, const __grid_constant__ CtrA
             const uint32_t s1 = __byte_perm((uint32_t)hi, 0, 0x0123) ^ ks.rk[1];
             const uint32_t s2 = __byte_perm((uint32_t)(lo >> 32), 0, 0x0123) ^ ks.rk[2];
             const uint32_t s3 = __byte_perm((uint32_t)lo, 0, 0x0123) ^ ks.rk[3];   /* byte 3 varies per block */
-            C0 = TB(OFF_T0, 0, s0) ^ TB(OFF_T1, 1, s1) ^ TB(OFF_T2, 2, s2) ^ ks.rk[4];
-            const uint32_t X1 = TB(OFF_T0, 0, s1) ^ TB(OFF_T1, 1, s2) ^ TB(OFF_T2, 2, s3) ^ TB(OFF_T3, 3, s0) ^ ks.rk[5];
-            const uint32_t X2 = TB(OFF_T0, 0, s2) ^ TB(OFF_T1, 1, s3) ^ TB(OFF_T2, 2, s0) ^ TB(OFF_T3, 3, s1) ^ ks.rk[6];
-            const uint32_t X3 = TB(OFF_T0, 0, s3) ^ TB(OFF_T1, 1, s0) ^ TB(OFF_T2, 2, s1) ^ TB(OFF_T3, 3, s2) ^ ks.rk[7];
-            D0 = TB(OFF_T1, 1, X1) ^ TB(OFF_T2, 2, X2) ^ TB(OFF_T3, 3, X3) ^ ks.rk[8];
-            D1 = TB(OFF_T0, 0, X1) ^ TB(OFF_T1, 1, X2) ^ TB(OFF_T2, 2, X3) ^ ks.rk[9];
-            D2 = TB(OFF_T0, 0, X2) ^ TB(OFF_T1, 1, X3) ^ TB(OFF_T3, 3, X1) ^ ks.rk[10];
-            D3 = TB(OFF_T0, 0, X3) ^ TB(OFF_T2, 2, X1) ^ TB(OFF_T3, 3, X2) ^ ks.rk[11];
+            C0 = TBL(0, 0, s0) ^ TBL(1, 1, s1) ^ TBL(2, 2, s2) ^ ks.rk[4];
+            const uint32_t X1 = TBL(0, 0, s1) ^ TBL(1, 1, s2) ^ TBL(2, 2, s3) ^ TBL(3, 3, s0) ^ ks.rk[5];
+            const uint32_t X2 = TBL(0, 0, s2) ^ TBL(1, 1, s3) ^ TBL(2, 2, s0) ^ TBL(3, 3, s1) ^ ks.rk[6];
+            const uint32_t X3 = TBL(0, 0, s3) ^ TBL(1, 1, s0) ^ TBL(2, 2, s1) ^ TBL(3, 3, s2) ^ ks.rk[7];
+            D0 = TBL(1, 1, X1) ^ TBL(2, 2, X2) ^ TBL(3, 3, X3) ^ ks.rk[8];
+            D1 = TBL(0, 0, X1) ^ TBL(1, 1, X2) ^ TBL(2, 2, X3) ^ ks.rk[9];
+            D2 = TBL(0, 0, X2) ^ TBL(1, 1, X3) ^ TBL(3, 3, X1) ^ ks.rk[10];
+            D3 = TBL(0, 0, X3) ^ TBL(2, 2, X1) ^ TBL(3, 3, X2) ^ ks.rk[11];
         }
 
         const uint64_t v0 = chunk * (uint64_t)(a.gpc * 256u);   /* first virtual index */
