@@ -78,8 +78,16 @@ constexpr int kMaxGroupsPerChunk = 8;          /* CTR: groups handled per warp t
 struct AesSched { uint32_t rk[60]; };
 
 /* byte offsets of the tables inside dynamic shared memory */
+#ifndef BC_NO_REPLICATION
+#define BC_NO_REPLICATION 0   /* A/B knob: plain 1 KB tables, 32 random indices collide in the banks */
+#endif
+#if BC_NO_REPLICATION
+constexpr int OFF_T0 = 0, OFF_T1 = 1024, OFF_T2 = 2048, OFF_T3 = 3072;
+constexpr int OFF_SB = 4096;
+#else
 constexpr int OFF_T0 = 0, OFF_T1 = 128, OFF_T2 = kArrayBytes, OFF_T3 = kArrayBytes + 128;
 constexpr int OFF_SB = 2 * kArrayBytes;
+#endif
 
 __device__ __forceinline__ uint32_t rotl32(uint32_t v, int n) { return __funnelshift_l(v, v, n); }
 __device__ __forceinline__ uint32_t xtime8(uint32_t x) { return ((x << 1) ^ ((x & 0x80u) ? 0x1bu : 0u)) & 0xffu; }
@@ -101,6 +109,14 @@ __device__ __forceinline__ uint32_t rt0_word(uint32_t i)
 template <bool DEC>
 __device__ __forceinline__ void fill_tables(uint32_t *sm)
 {
+#if BC_NO_REPLICATION
+    for (uint32_t i = threadIdx.x; i < 256u; i += blockDim.x) {
+        uint32_t w = DEC ? rt0_word(i) : ft0_word(i);
+        sm[i] = w; sm[256 + i] = rotl32(w, 8); sm[512 + i] = rotl32(w, 16); sm[768 + i] = rotl32(w, 24);
+        if (DEC) sm[1024 + i] = (uint32_t)c_inv_sbox[i] * 0x01010101u;
+    }
+    return;
+#endif
     for (uint32_t idx = threadIdx.x; idx < 256u * 32u; idx += blockDim.x) {
         uint32_t i = idx >> 5, l = idx & 31u;   /* i is warp-uniform: constant-cache broadcast */
         uint32_t w = DEC ? rt0_word(i) : ft0_word(i);
@@ -116,7 +132,12 @@ __device__ __forceinline__ void fill_tables(uint32_t *sm)
 template <int K>
 __device__ __forceinline__ uint32_t baddr(uint32_t x, uint32_t lane4)
 {
+#if BC_NO_REPLICATION
+    (void)lane4;
+    return ((x >> (8 * K)) & 0xffu) << 2;
+#else
     return __byte_perm(x, lane4, 0x5504 | (K << 4));
+#endif
 }
 
 template <int OFF>
@@ -282,7 +303,7 @@ aes_ctr_kernel(const __grid_constant__ AesSched ks, const __grid_constant__ CtrA
     uint32_t f3[kRowsPerGroup];
 #pragma unroll
     for (int it = 0; it < kRowsPerGroup; it++)
-        f3[it] = lds32<OFF_T3>(tb.base + (((((uint32_t)it * 32u + lane) ^ k3) & 0xffu) << 8 | tb.lane4));
+        f3[it] = TBL(3, 0, ((uint32_t)it * 32u + lane) ^ k3);
     /* the fast path walks rows in order, so the values rotate through f3[0..] instead of being indexed */
 #define F3(k) f3[k]
 #define F3_ROTATE()                                                                      \
