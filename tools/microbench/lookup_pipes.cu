@@ -75,6 +75,42 @@ __global__ void __launch_bounds__(THREADS, 1) k_lop3(uint32_t *out, long long *c
     if (threadIdx.x == 0) cycles[blockIdx.x] = t1 - t0;
 }
 
+// Peak rate of conflict-free 32-bit shared-memory lookups: 16 independent lookups per trip from 16
+// index registers (the shape of one AES round), results folded with LOP3.
+__global__ void __launch_bounds__(THREADS, 1) k_lds_peak(const uint32_t *gtab, uint32_t *out, long long *cycles)
+{
+    extern __shared__ uint32_t sm[];
+    for (int i = threadIdx.x; i < 256 * 32; i += THREADS) sm[i] = gtab[i >> 5];
+    __syncthreads();
+    // same layout and addressing as the AES kernels: entry i of lane L at byte i*128 + L*4 here
+    // (one table), address = one PRMT (index byte -> bits 7.., needs a shift) -- use the 256-byte
+    // row variant instead: rows of 256 B, only the first 128 B used, so the index lands in byte 1
+    __syncthreads();
+    for (int i = threadIdx.x; i < 256 * 32; i += THREADS) sm[(i >> 5) * 64 + (i & 31)] = gtab[i >> 5];
+    __syncthreads();
+    const uint32_t lane4 = (threadIdx.x & 31) * 4;
+    const uint32_t base = (uint32_t)__cvta_generic_to_shared(sm);
+    uint32_t s[4] = { threadIdx.x * 2654435761u, threadIdx.x * 40503u + 1, threadIdx.x * 9176u + 7, threadIdx.x + 99u };
+    auto look = [&](uint32_t x, int k) {
+        uint32_t a = __byte_perm(x, lane4, 0x5504 | (k << 4)), v;
+        asm volatile("ld.shared.u32 %0, [%1];" : "=r"(v) : "r"(base + a));
+        return v;
+    };
+    long long t0 = clock64();
+#pragma unroll 1
+    for (int it = 0; it < ITERS; it++) {
+        uint32_t t[4];
+#pragma unroll
+        for (int c = 0; c < 4; c++)
+            t[c] = look(s[c], 0) ^ look(s[(c + 1) & 3], 1) ^ look(s[(c + 2) & 3], 2) ^ look(s[(c + 3) & 3], 3);
+#pragma unroll
+        for (int c = 0; c < 4; c++) s[c] = t[c];
+    }
+    long long t1 = clock64();
+    out[blockIdx.x * THREADS + threadIdx.x] = s[0] ^ s[1] ^ s[2] ^ s[3];
+    if (threadIdx.x == 0) cycles[blockIdx.x] = t1 - t0;
+}
+
 template <int MODE, int RATIO>
 int run(const char *name, cudaTextureObject_t tex, uint32_t *gtab, uint32_t *out, long long *cyc, int sms)
 {
@@ -116,6 +152,15 @@ int main()
         long long c0; cudaMemcpy(&c0, cyc, 8, cudaMemcpyDeviceToHost);
         double ops = 8.0 * 16 * ITERS * THREADS;
         printf("%-34s cycles %10lld  LOP3 lane-ops/clk/SM %6.2f\n", "LOP3 only (8 chains)", c0, ops / (double)c0);
+    }
+    CK(cudaFuncSetAttribute(k_lds_peak, cudaFuncAttributeMaxDynamicSharedMemorySize, 65536));
+    k_lds_peak<<<sms, THREADS, 65536>>>(gtab, out, cyc);
+    CK(cudaDeviceSynchronize());
+    k_lds_peak<<<sms, THREADS, 65536>>>(gtab, out, cyc);
+    CK(cudaDeviceSynchronize());
+    {
+        long long c0; cudaMemcpy(&c0, cyc, 8, cudaMemcpyDeviceToHost);
+        printf("%-34s cycles %10lld  lookups/clk/SM %6.2f\n", "LDS peak (16 independent/trip)", c0, 16.0 * ITERS * THREADS / (double)c0);
     }
     run<0, 4>("LDS only (16/trip)", tex, gtab, out, cyc, sms);
     run<1, 1>("TEX only (4/trip)", tex, gtab, out, cyc, sms);
