@@ -496,11 +496,11 @@ aes_blocks_kernel(const __grid_constant__ AesSched ks, const __grid_constant__ B
                 /* out of place nothing overwrites the input: C_{i-1} is one more (cache-resident) load,
                  * cheaper on the shared data pipe than eight shuffles per row */
                 if (live) prev = (b == 0) ? a.iv : a.in[b - 1];
-            } else if (CHAIN) {                    /* in place: the lane to the left, lane 0 from the previous row */
-                prev.x = __shfl_up_sync(0xffffffffu, c.x, 1);
-                prev.y = __shfl_up_sync(0xffffffffu, c.y, 1);
-                prev.z = __shfl_up_sync(0xffffffffu, c.z, 1);
-                prev.w = __shfl_up_sync(0xffffffffu, c.w, 1);
+            } else if (CHAIN) {
+                /* in place: a row's loads all come before its stores, so the lane to the left can
+                 * still be read from memory; only lane 0 needs the previous row's last block, which
+                 * that row's store has already overwritten — it travels in `carry` */
+                if (live && lane != 0) prev = a.in[b - 1];
                 if (lane == 0) prev = carry;
                 carry.x = __shfl_sync(0xffffffffu, c.x, 31);
                 carry.y = __shfl_sync(0xffffffffu, c.y, 31);
