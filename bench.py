@@ -17,7 +17,12 @@ D2H inside the timed region); `roofline` is for the dominant kernel
 (aes_ctr_kernel<10>) against the measured HBM copy bandwidth with 2 algorithmic
 bytes of HBM traffic per plaintext byte; `cpu_baseline` is the reference's
 aesni.c AES_CTR_encrypt (oracle/_ref, built from the unmodified sources) on all
-host cores over a bounded sample.  oracle/ is used only as that CPU baseline.
+host cores over a bounded sample.  At N > 1 the line also carries `config5`:
+BASELINE configs[4] as written (256 GiB sharded by counter offset over the N
+GPUs, filled on the device by a generator the host can replay, encrypted, and a
+stratified sample of windows — shard ends, every 64 GiB seam, random — compared
+with the reference's aes.c outside the timed region).  oracle/ is used only as
+the CPU baseline and as that checker, never inside a timed region.
 """
 from __future__ import annotations
 
@@ -59,6 +64,61 @@ def profile_traffic():
         return j.get("dram_bytes_per_launch_4gib")
     except Exception:
         return None
+
+
+SEED = 1337                                                     # srand(1337), aes-modes/test.c:354
+M64 = (1 << 64) - 1
+
+
+def splitmix_bytes(first_word: int, n_words: int) -> np.ndarray:
+    """Host replay of bc_fill_splitmix64_dev (include/bulkcipher.h): bytes of words [first_word, +n_words)."""
+    with np.errstate(over="ignore"):
+        z = (np.arange(n_words, dtype=np.uint64) + np.uint64((SEED + first_word) & M64)) + np.uint64(0x9E3779B97F4A7C15)
+        z = (z ^ (z >> np.uint64(30))) * np.uint64(0xBF58476D1CE4E5B9)
+        z = (z ^ (z >> np.uint64(27))) * np.uint64(0x94D049BB133111EB)
+        z = z ^ (z >> np.uint64(31))
+    return z.view(np.uint8)
+
+
+def checker():
+    """The CPU checker for spot checks OUTSIDE timed regions: the reference's own aes.c
+    (oracle/_ref/libref.so) when it travelled, else the oracle port."""
+    import oracle
+
+    return (oracle.Ref(), "oracle/_ref aes.c aes_crypt_ctr") if oracle.Ref.available() else (oracle.Oracle(), "oracle.c port")
+
+
+def verify_ctr_windows(chk, d_cipher, shard_first_word: int, shard_first_block: int, offsets, win: int) -> int:
+    """d_cipher (device tensor, this rank's shard) must equal splitmix plaintext XOR the reference's
+    AES-128-CTR keystream at every window [off, off+win).  Returns the number of windows checked."""
+    base = int.from_bytes(COUNTER, "big")
+    for off in offsets:
+        got = d_cipher[off:off + win].cpu().numpy()
+        plain = splitmix_bytes(shard_first_word + off // 8, win // 8)
+        nc = ((base + shard_first_block + off // 16) % (1 << 128)).to_bytes(16, "big")
+        want = chk.aes_ctr(KEY, nc, plain)[0]
+        if not np.array_equal(got, want):
+            bad = int(np.flatnonzero(got != want)[0])
+            raise SystemExit(f"PARITY FAILURE: window at shard byte {off} differs from the reference at byte {bad}")
+    return len(offsets)
+
+
+def host_facts(L, local: int):
+    nodes = 0
+    try:
+        nodes = len([d for d in os.listdir("/sys/devices/system/node") if d.startswith("node") and d[4:].isdigit()])
+    except OSError:
+        pass
+    mem_gib = None
+    try:
+        with open("/proc/meminfo") as f:
+            for ln in f:
+                if ln.startswith("MemAvailable:"):
+                    mem_gib = int(ln.split()[1]) >> 20
+    except OSError:
+        pass
+    return {"cpus": cpu_threads(), "numa_nodes": nodes, "gpu_numa_node": int(L.bc_device_numa_node(local)),
+            "mem_available_gib": mem_gib}
 
 
 class ClockSampler:
@@ -211,7 +271,7 @@ def run_reference(args):
         return 0
     threads = cpu_threads()
     t_all0 = time.perf_counter()
-    r = ReferenceCtr(2 * GIB, threads)
+    r = ReferenceCtr(SHARD_BYTES, threads)
     for _ in range(args.warmup):
         r.one_pass()
     t0 = time.perf_counter()
@@ -224,8 +284,8 @@ def run_reference(args):
         "steps": args.steps, "warmup": args.warmup, "ms_per_step": round(dt / args.steps * 1e3, 3),
         "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "u32", "data": "synthetic",
         "config": {"workload": "AES-128-CTR encrypt, the reference's own CPU path on all host cores; each step a "
-                               f"bounded {r.nbytes >> 20} MiB sample of the 4 GiB-per-GPU workload", "key_bits": 128,
-                   "sample_bytes": r.nbytes},
+                               f"{r.nbytes >> 20} MiB = the whole 4 GiB-per-GPU workload", "key_bits": 128,
+                   "bytes_per_gpu": r.nbytes, "sample_bytes": r.nbytes},
         "cpu_baseline": {"value": round(value, 3), "unit": UNIT, "cores": threads, "kind": r.kind,
                          "sample": f"{r.what}; {r.nbytes >> 20} MiB per step split over {threads} threads"},
         "e2e": {"value": round(value, 3), "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
@@ -239,12 +299,16 @@ def run_reference(args):
 
 def link_probe(d_a, d_b):
     """What the host link allows for an in+out transfer: 1 GiB H2D and 1 GiB D2H at the same time
-    (pinned memory, monolithic copies), GB/s per direction.  The e2e figure cannot exceed it."""
+    (pinned memory, monolithic copies), GB/s per direction.  The e2e figure cannot exceed it.
+    Under torchrun every rank runs this at the same moment (the caller puts a barrier in front),
+    so the figure is what the box gives each GPU when all N links are busy at once."""
     import torch
 
     n = min(GIB, d_a.numel())
     h_a = torch.empty(n, dtype=torch.uint8, pin_memory=True)
     h_b = torch.empty(n, dtype=torch.uint8, pin_memory=True)
+    h_a.fill_(3)
+    h_b.fill_(5)
     s1, s2 = torch.cuda.Stream(), torch.cuda.Stream()
     best = 1e9
     for _ in range(3):
@@ -265,39 +329,58 @@ def link_probe(d_a, d_b):
     return n / best / 1e6
 
 
-def other_workloads(pkg, L, d_in, d_out, st, hbm_peak):
-    """BASELINE configs 3 and 4 (and the metric's "batched RC4 GB/s"), device resident on 4 GiB:
-    best-of-5 CUDA-event time per launch, GB/s of plaintext and the HBM fraction at the
-    algorithmic 2 bytes of traffic per byte.  Reported next to the headline, not instead of it."""
+class Ranks:
+    """The only cross-rank traffic of the bench: a barrier and MAX / MIN / SUM of a few floats
+    (timings).  No collective touches cipher data."""
+
+    def __init__(self, distributed: bool):
+        self.on = distributed
+
+    def barrier(self):
+        import torch
+        import torch.distributed as dist
+
+        torch.cuda.synchronize()
+        if self.on:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    def reduce(self, values, op: str):
+        import torch
+        import torch.distributed as dist
+
+        if not self.on:
+            return [float(v) for v in values]
+        t = torch.tensor([float(v) for v in values], device="cuda", dtype=torch.float64)
+        dist.all_reduce(t, op={"max": dist.ReduceOp.MAX, "min": dist.ReduceOp.MIN, "sum": dist.ReduceOp.SUM}[op])
+        return [float(x) for x in t.cpu()]
+
+
+def other_workloads(pkg, L, d_in, d_out, st, hbm_peak, ranks: Ranks, n_gpus: int, rank: int):
+    """BASELINE configs 3 and 4 (and the metric's "batched RC4 GB/s"), device resident on 4 GiB per
+    GPU, EVERY rank on its own shard (messages / streams / blocks [rank*n, (rank+1)*n) of the job):
+    K launches back to back between two CUDA events after a barrier, MAX over ranks; value = all
+    ranks' plaintext bytes over that time, hbm_frac per GPU at the algorithmic 2 bytes of traffic
+    per byte.  Reported next to the headline, not instead of it."""
     import torch
 
     n = d_in.numel()
     key32 = bytes(range(32))
+    K = 5
 
     def sched(key, enc=True):
         rc, ctx = (pkg.aes_setkey_enc if enc else pkg.aes_setkey_dec)(key)
         return pkg.schedule_words(ctx), ctx.nr
-
-    def best_ms(fn, iters=5):
-        fn()
-        torch.cuda.synchronize()
-        best = 1e9
-        for _ in range(iters):
-            a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-            a.record()
-            fn()
-            b.record()
-            torch.cuda.synchronize()
-            best = min(best, a.elapsed_time(b))
-        return best
 
     e256, nr = sched(key32)
     d256, _ = sched(key32, enc=False)
     iv = bytes(range(16))
     n_msgs = n // 65536
     n_streams = n // 4096
-    d_iv = torch.randint(0, 256, (n_msgs * 16,), dtype=torch.uint8, device="cuda")
-    d_keys = torch.randint(0, 256, (n_streams * 16,), dtype=torch.uint8, device="cuda")
+    g = torch.Generator(device="cuda")
+    g.manual_seed(4242 + rank)
+    d_iv = torch.randint(0, 256, (n_msgs * 16,), dtype=torch.uint8, device="cuda", generator=g)
+    d_keys = torch.randint(0, 256, (n_streams * 16,), dtype=torch.uint8, device="cuda", generator=g)
     ip, op = d_in.data_ptr(), d_out.data_ptr()
     runs = {
         "aes256_ecb_encrypt_4gib": (lambda: pkg.check(L.bc_aes_ecb_dev(e256.ctypes.data, nr, 1, ip, op, n, st)), 2.0 * n),
@@ -312,26 +395,112 @@ def other_workloads(pkg, L, d_in, d_out, st, hbm_peak):
     }
     out = {}
     for name, (fn, traffic) in runs.items():
-        ms = best_ms(fn)
-        out[name] = {"value": round(n / ms / 1e6, 1), "unit": UNIT, "kernel_ms": round(ms, 4),
-                     "hbm_frac": round(traffic / ms / 1e6 / hbm_peak, 4)}
-    # batched RC4 end to end: pinned host buffers through bc_arc4_batch_host (1 GiB = 2^18 streams x 4 KiB)
+        fn()
+        fn()
+        ranks.barrier()
+        a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        a.record()
+        for _ in range(K):
+            fn()
+        b.record()
+        torch.cuda.synchronize()
+        ms = ranks.reduce([a.elapsed_time(b) / K], "max")[0]
+        out[name] = {"value": round(n_gpus * n / ms / 1e6, 1), "unit": UNIT, "kernel_ms": round(ms, 4),
+                     "hbm_frac": round(traffic / ms / 1e6 / hbm_peak, 4), "per_gpu_bytes": n, "launches": K}
+    # batched RC4 end to end: pinned host buffers through bc_arc4_batch_host (1 GiB = 2^18 streams x 4 KiB per GPU)
     hn = GIB
     h_in, h_out, h_keys = L.bc_host_alloc(hn), L.bc_host_alloc(hn), L.bc_host_alloc((hn // 4096) * 16)
     if h_in and h_out and h_keys:
         np.ctypeslib.as_array((ctypes.c_ubyte * hn).from_address(h_in))[:] = 0x5A
         np.ctypeslib.as_array((ctypes.c_ubyte * ((hn // 4096) * 16)).from_address(h_keys))[:] = np.resize(
-            np.frombuffer(np.random.default_rng(5).bytes(1 << 20), dtype=np.uint8), (hn // 4096) * 16)
-        ts = []
-        for _ in range(4):
-            t0 = time.perf_counter()
+            np.frombuffer(np.random.default_rng(5 + rank).bytes(1 << 20), dtype=np.uint8), (hn // 4096) * 16)
+        pkg.check(L.bc_arc4_batch_host(hn // 4096, h_keys, 16, 4096, h_in, h_out, None, None))
+        ranks.barrier()
+        t0 = time.perf_counter()
+        for _ in range(3):
             pkg.check(L.bc_arc4_batch_host(hn // 4096, h_keys, 16, 4096, h_in, h_out, None, None))
-            ts.append(time.perf_counter() - t0)
-        out["rc4_batched_host_buffers_1gib"] = {"value": round(hn / min(ts[1:]) / 1e9, 2), "unit": UNIT,
-                                                 "api": "bc_arc4_batch_host (pinned buffers, H2D + kernel + D2H)"}
+        dt = ranks.reduce([time.perf_counter() - t0], "max")[0]
+        out["rc4_batched_host_buffers_1gib"] = {"value": round(n_gpus * hn * 3 / dt / 1e9, 2), "unit": UNIT,
+                                                 "api": "bc_arc4_batch_host (pinned buffers, H2D + kernel + D2H), 1 GiB per GPU"}
     for p in (h_in, h_out, h_keys):
         L.bc_host_free(p)
     return out
+
+
+def run_config5(pkg, L, rk, nr, st, ranks: Ranks, n_gpus: int, rank: int, steps: int):
+    """BASELINE configs[4] as written: AES-128-CTR over a 256 GiB logical buffer, GPU g of N owning
+    bytes [g*256/N GiB, (g+1)*256/N GiB) with its counter offset by its first block index.  The
+    buffer is generated in HBM (bc_fill_splitmix64_dev, seed 1337 + logical word index), so the host
+    can replay any window; where input + output do not both fit (N = 2: 128 GiB per GPU) the shard
+    is encrypted in place.  After the timed steps the shard is regenerated, encrypted once more and
+    a stratified sample of 64 KiB windows — both shard ends, a window across every 64 GiB seam (the
+    2^32-block carry into counter byte 11, aes.c:884-888), 32 random ones — is compared with the
+    reference's aes.c, outside the timed region."""
+    import torch
+
+    total = 256 * GIB
+    shard = total // n_gpus
+    free_b, _ = torch.cuda.mem_get_info()
+    in_place = 2 * shard > 0.92 * free_b
+    if shard > 0.95 * free_b:
+        return {"skipped": f"a {shard >> 30} GiB shard does not fit in {free_b >> 30} GiB of free HBM"}
+    d_a = torch.empty(shard, dtype=torch.uint8, device="cuda")
+    d_b = d_a if in_place else torch.empty(shard, dtype=torch.uint8, device="cuda")
+    first_word = rank * (shard // 8)
+    first_block = rank * (shard // 16)
+
+    def fill():
+        pkg.check(L.bc_fill_splitmix64_dev(d_a.data_ptr(), shard, SEED, first_word, st))
+
+    def step():
+        pkg.check(L.bc_aes_ctr_dev(rk.ctypes.data, nr, COUNTER, 128, first_block, d_a.data_ptr(), d_b.data_ptr(),
+                                   shard, None, st))
+
+    fill()
+    for _ in range(2):
+        step()
+    ranks.barrier()
+    a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    a.record()
+    for _ in range(steps):
+        step()
+    b.record()
+    ranks.barrier()
+    ms = ranks.reduce([a.elapsed_time(b)], "max")[0]
+
+    # ---- verification, outside the timed region
+    fill()
+    step()
+    torch.cuda.synchronize()
+    win = 65536
+    offs = {0, shard - win}
+    seam = 64 * GIB
+    lo, hi = rank * shard, (rank + 1) * shard
+    n_seams = 0
+    for k in range(1, total // seam):
+        pos = k * seam
+        if lo < pos < hi:                                         # seam inside the shard: straddle it
+            offs.add(pos - lo - win // 2)
+            n_seams += 1
+        elif pos == lo:                                           # seam at the shard start: the carry (byte pos + 256) is in window 0
+            n_seams += 1
+    rng = np.random.default_rng(1000 + rank)
+    for r in rng.integers(0, (shard - win) // 16, 32):
+        offs.add(int(r) * 16)
+    chk, chk_name = checker()
+    t0 = time.perf_counter()
+    n_checked = verify_ctr_windows(chk, d_b, first_word, first_block, sorted(offs), win)
+    verify_s = time.perf_counter() - t0
+    tot_windows, tot_seams = ranks.reduce([n_checked, n_seams], "sum")
+    del d_a, d_b
+    torch.cuda.empty_cache()
+    return {"workload": f"AES-128-CTR over a 256 GiB logical buffer sharded by counter offset over {n_gpus} GPUs "
+                        "(BASELINE configs[4]); generated on the device, host-replayable",
+            "value": round(total * steps / (ms * 1e-3) / 1e9, 1), "unit": UNIT, "ms_per_step": round(ms / steps, 3),
+            "steps": steps, "bytes_per_gpu": shard, "in_place": bool(in_place),
+            "verified_windows": int(tot_windows), "window_bytes": win, "seam_windows": int(tot_seams),
+            "verified_against": chk_name, "verify_s_rank0": round(verify_s, 2),
+            "hbm_frac_per_gpu": round(2.0 * shard * steps / (ms * 1e-3) / 1e9 / measured_peak()[0], 4)}
 
 
 def run_ours(args):
@@ -351,6 +520,7 @@ def run_ours(args):
         os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
         dist.init_process_group("nccl", device_id=torch.device("cuda", local))
     n_gpus = world if distributed else 1
+    ranks = Ranks(distributed)
 
     pkg = g.load_package()
     if not os.path.exists(pkg.LIB_PATH) and rank == 0:
@@ -359,30 +529,31 @@ def run_ours(args):
         dist.barrier()
     L = pkg.lib()
     pkg.check(L.bc_set_device(local))
+    # host-side locality before any pinned allocation: this rank's thread (and the pages it
+    # touches) go to the NUMA node its GPU hangs off; a no-op on single-node boxes
+    if not args.no_numa_bind:
+        L.bc_bind_host_thread_to_device(local)
+    facts = host_facts(L, local)
     rc, ctx = pkg.aes_setkey_enc(KEY)
     rk = pkg.schedule_words(ctx)
     nr = ctx.nr
     nbytes = int(args.shard_gib * GIB) // 65536 * 65536
     blocks = nbytes // 16
     first_block = rank * blocks                                   # shard by counter offset
-
-    d_in = torch.empty(nbytes, dtype=torch.uint8, device="cuda")                 # synthetic random plaintext
-    for off in range(0, nbytes, 4 * GIB):
-        d_in[off:off + 4 * GIB].random_(0, 256)
-    in_place = nbytes > 48 * GIB                                                 # config 5 at 2 GPUs: 128 GiB per GPU
-    d_out = d_in if in_place else torch.empty_like(d_in)
+    first_word = rank * (nbytes // 8)
     st = torch.cuda.current_stream().cuda_stream
+
+    d_in = torch.empty(nbytes, dtype=torch.uint8, device="cuda")
+    # synthetic plaintext generated in HBM, replayable on the host (checked below against the reference)
+    pkg.check(L.bc_fill_splitmix64_dev(d_in.data_ptr(), nbytes, SEED, first_word, st))
+    in_place = nbytes > 48 * GIB
+    d_out = d_in if in_place else torch.empty_like(d_in)
 
     def step():
         pkg.check(L.bc_aes_ctr_dev(rk.ctypes.data, nr, COUNTER, 128, first_block, d_in.data_ptr(), d_out.data_ptr(),
                                    nbytes, None, st))
 
-    def barrier():
-        torch.cuda.synchronize()
-        if distributed:
-            dist.barrier()
-        torch.cuda.synchronize()
-
+    barrier = ranks.barrier
     for _ in range(args.warmup):
         step()
     sampler = ClockSampler(local)
@@ -412,17 +583,27 @@ def run_ours(args):
         torch.cuda.synchronize()
     soak_t1 = time.time()
     clocks = sampler.stop(t0, soak_t1) if rank == 0 else None
-    if distributed:
-        t = torch.tensor([total_ms, kernel_ms], device="cuda", dtype=torch.float64)
-        dist.all_reduce(t, op=dist.ReduceOp.MAX)
-        total_ms, kernel_ms = float(t[0]), float(t[1])
+    total_ms, kernel_ms = ranks.reduce([total_ms, kernel_ms], "max")
+
+    # ---- parity of the timed output, outside the timed region: three 64 KiB windows of this rank's
+    # ciphertext (first — it holds the 2^32 counter carry at block 16 —, middle, last) against the
+    # reference's aes.c on the replayed plaintext
+    parity = None
+    if not in_place and (args.steps + args.warmup) > 0:
+        chk, chk_name = checker()
+        win = 65536
+        offs = [0, (nbytes // 2) // win * win, nbytes - win]
+        n_ok = verify_ctr_windows(chk, d_out, first_word, first_block, offs, win)
+        parity = {"windows": int(ranks.reduce([n_ok], "sum")[0]), "window_bytes": win, "against": chk_name,
+                  "what": "timed device-resident output vs the reference on the replayed splitmix plaintext"}
 
     # ---- e2e: the host-buffer C-ABI call, pinned host memory, H2D + kernel + D2H every step.
-    # The 4 GiB shard streams through a pinned window; at N <= 2 the window is the whole shard,
-    # at N > 2 it is 1 GiB walked four times with the counter offset advancing (same bytes over
-    # the link per step, 2 GiB instead of 8 GiB of pinned host memory per rank).
+    # The 4 GiB shard streams through a pinned window: the whole shard when the host has room for
+    # 2 x 4 GiB of pinned memory per rank, else 1 GiB walked four times with the counter offset
+    # advancing (same bytes over the link per step).
     e2e_bytes = min(nbytes, SHARD_BYTES)
-    window = e2e_bytes if n_gpus <= 2 else GIB
+    roomy = (facts.get("mem_available_gib") or 0) >= 2 * n_gpus * (2 * e2e_bytes >> 30) + 16
+    window = e2e_bytes if (n_gpus <= 2 or roomy) else GIB
     h_in = h_out = None
     while window >= (64 << 20):
         h_in, h_out = L.bc_host_alloc(window), L.bc_host_alloc(window)
@@ -437,6 +618,7 @@ def run_ours(args):
     passes = e2e_bytes // window
     hin = np.ctypeslib.as_array((ctypes.c_ubyte * window).from_address(h_in))
     hin[:] = np.resize(np.frombuffer(np.random.default_rng(7 + rank).bytes(1 << 24), dtype=np.uint8), window)
+    np.ctypeslib.as_array((ctypes.c_ubyte * window).from_address(h_out))[:] = 0      # first touch before timing
     last = np.zeros(16, np.uint8)
 
     def e2e_step():
@@ -451,32 +633,49 @@ def run_ours(args):
     for _ in range(e2e_steps):
         e2e_step()
     barrier()
-    e2e_s = time.perf_counter() - w0
-    if distributed:
-        t = torch.tensor([e2e_s], device="cuda", dtype=torch.float64)
-        dist.all_reduce(t, op=dist.ReduceOp.MAX)
-        e2e_s = float(t[0])
-    # spot-check the e2e output (last window) against the device-resident path on the same counter stream
+    e2e_s = ranks.reduce([time.perf_counter() - w0], "max")[0]
+    # spot-check the e2e output (last window): the device-resident path on the same counter stream, and the reference
     d_chk = torch.from_numpy(hin[: 1 << 20].copy()).cuda()
     d_chk_out = torch.empty_like(d_chk)
-    pkg.check(L.bc_aes_ctr_dev(rk.ctypes.data, nr, COUNTER, 128, first_block + (passes - 1) * (window // 16),
-                               d_chk.data_ptr(), d_chk_out.data_ptr(), 1 << 20, None, st))
+    fb_last = first_block + (passes - 1) * (window // 16)
+    pkg.check(L.bc_aes_ctr_dev(rk.ctypes.data, nr, COUNTER, 128, fb_last, d_chk.data_ptr(), d_chk_out.data_ptr(), 1 << 20, None, st))
     torch.cuda.synchronize()
     hout = np.ctypeslib.as_array((ctypes.c_ubyte * (1 << 20)).from_address(h_out))
     if not np.array_equal(hout, d_chk_out.cpu().numpy()):
         raise SystemExit("e2e output differs from the device-resident path")
+    chk, _ = checker()
+    nc = ((int.from_bytes(COUNTER, "big") + fb_last) % (1 << 128)).to_bytes(16, "big")
+    if not np.array_equal(hout[:65536], chk.aes_ctr(KEY, nc, hin[:65536])[0]):
+        raise SystemExit("PARITY FAILURE: e2e output differs from the reference")
     L.bc_host_free(h_in)
     L.bc_host_free(h_out)
+
+    # ---- what the host links allow with all N GPUs copying in and out at once
+    link = None
+    if not in_place:
+        try:
+            barrier()
+            mine = link_probe(d_in, d_out)
+            link = {"min": ranks.reduce([mine], "min")[0], "sum": ranks.reduce([mine], "sum")[0]}
+        except Exception as e:  # noqa: BLE001
+            link = {"error": str(e)}
+
+    # ---- the rest of BASELINE.json's metric / configs, device resident, every rank on its own GPU
+    others = None
+    if not args.no_others and not in_place and nbytes == SHARD_BYTES:
+        others = other_workloads(pkg, L, d_in, d_out, st, measured_peak()[0], ranks, n_gpus, rank)
+
+    # ---- BASELINE configs[4] as written (N > 1): 256 GiB over the N GPUs, verified
+    config5 = None
+    if n_gpus > 1 and not args.no_config5 and nbytes == SHARD_BYTES:
+        del d_in, d_out
+        torch.cuda.empty_cache()
+        config5 = run_config5(pkg, L, rk, nr, st, ranks, n_gpus, rank, max(2, min(args.steps, 5)))
 
     if rank != 0:
         if distributed:
             dist.destroy_process_group()
         return 0
-
-    # ---- the rest of BASELINE.json's metric / configs, device resident, on this rank's GPU
-    others = None
-    if not args.no_others and not in_place and nbytes == SHARD_BYTES:
-        others = other_workloads(pkg, L, d_in, d_out, st, measured_peak()[0])
 
     peak, peak_src = measured_peak()
     value = n_gpus * nbytes * args.steps / (total_ms * 1e-3) / 1e9
@@ -490,10 +689,12 @@ def run_ours(args):
         "warmup": args.warmup, "ms_per_step": round(total_ms / args.steps, 4), "higher_is_better": True,
         "scaling": "weak", "vs_baseline": None, "dtype": "u32", "data": "synthetic",
         "config": {"workload": f"AES-128-CTR encrypt of a {nbytes / GIB:g} GiB synthetic buffer per GPU "
-                               "(BASELINE configs[1] at 4 GiB; configs[4] with --shard-gib 256/N); "
-                               "N GPUs shard by counter offset, no collective",
+                               "(BASELINE configs[1] at 4 GiB); N GPUs shard by counter offset, no collective; "
+                               "configs[4] (256 GiB over N GPUs) is the `config5` record at N > 1",
                    "key_bits": 128, "bytes_per_gpu": nbytes, "counter": COUNTER.hex(),
-                   "l2": "inputs (>= 4 GiB) larger than L2 (126 MB); no flush needed", "in_place": in_place},
+                   "input": "bc_fill_splitmix64_dev(seed 1337): generated in HBM, replayable on the host",
+                   "l2": "inputs (>= 4 GiB) larger than L2 (126 MB); no flush needed", "in_place": in_place,
+                   "host": facts},
         "roofline": {"bound": "hbm", "achieved": round(achieved, 1), "peak": peak, "unit": "GB/s",
                      "frac": round(achieved / peak, 4), "traffic": profile_traffic(),
                      "kernel": "aes_ctr_kernel<10,1024>", "kernel_ms": round(kernel_ms, 4), "peak_source": peak_src,
@@ -507,16 +708,20 @@ def run_ours(args):
                 "host_window_bytes": window, "calls_per_step": passes},
         "gpu_launches": args.steps, "clocks": clocks,
     }
+    if parity is not None:
+        line["parity_check"] = parity
     if others is not None:
         line["other_workloads"] = others
-    if n_gpus == 1 and not in_place:
-        try:
-            link = link_probe(d_in, d_out)
-            line["e2e"]["link_gbs_each_direction"] = round(link, 2)
-            line["e2e"]["frac_of_link"] = round(e2e_value / link, 4)
-            line["e2e"]["note"] = "host buffers in and out: bound by the PCIe link (H2D and D2H at once), not by the kernel"
-        except Exception as e:  # noqa: BLE001
-            line["e2e"]["note"] = f"link probe failed: {e}"
+    if config5 is not None:
+        line["config5"] = config5
+    if link and "error" not in link:
+        line["e2e"]["link_gbs_each_direction"] = round(link["min"], 2)
+        line["e2e"]["link_gbs_aggregate"] = round(link["sum"], 2)
+        line["e2e"]["frac_of_link"] = round(e2e_value / link["sum"], 4)
+        line["e2e"]["note"] = ("host buffers in and out: bound by the host links (H2D and D2H at once on all N GPUs, "
+                               "measured live with every rank copying at the same time), not by the kernel")
+    elif link:
+        line["e2e"]["note"] = f"link probe failed: {link['error']}"
     if n_gpus == 1 and not args.no_cpu_baseline:
         threads = cpu_threads()
         r = ReferenceCtr(2 * GIB, threads)
@@ -542,6 +747,8 @@ def main():
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-others", action="store_true", help="skip the configs 3/4 side measurements")
+    ap.add_argument("--no-config5", action="store_true", help="skip the 256 GiB configs[4] record at N > 1")
+    ap.add_argument("--no-numa-bind", action="store_true", help="A/B: leave the rank's host thread unbound")
     ap.add_argument("--shard-gib", type=float, default=4.0,
                     help="bytes per GPU in GiB (default 4 = BASELINE configs[1]; 256/N reproduces config 5)")
     args = ap.parse_args()
@@ -554,7 +761,8 @@ def main():
         cmd = [sys.executable, "-m", "torch.distributed.run", "--nnodes=1", f"--nproc-per-node={args.gpus}",
                "--master-addr", "127.0.0.1", "--master-port", os.environ.get("MASTER_PORT", "29511"), __file__,
                "--gpus", str(args.gpus), "--steps", str(args.steps), "--warmup", str(args.warmup),
-               "--shard-gib", str(args.shard_gib)] + (["--no-others"] if args.no_others else [])
+               "--shard-gib", str(args.shard_gib)] + (["--no-others"] if args.no_others else []) + \
+              (["--no-config5"] if args.no_config5 else []) + (["--no-numa-bind"] if args.no_numa_bind else [])
         return subprocess.call(cmd)
     return run_ours(args)
 

@@ -7,8 +7,10 @@
  * aes_context.rk[] slot back to back — SURVEY finding 2).
  *
  * The functions are `void` in the reference, so a GPU failure cannot be
- * returned: it is reported on stderr and the process aborts (no silent
- * garbage, no CPU fallback).  Use bulkcipher.h for error codes.
+ * returned: it is reported on stderr, the output buffer is left untouched (no
+ * silent garbage, no CPU fallback) and the code waits in bc_void_status()
+ * (bulkcipher.h); BULKCIPHER_ABORT_ON_ERROR=1 makes it abort() instead.  Use
+ * the bc_* calls of bulkcipher.h where a return code is wanted.
  */
 #ifndef BULKCIPHER_DROPIN_AESNI_H
 #define BULKCIPHER_DROPIN_AESNI_H

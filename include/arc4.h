@@ -23,7 +23,8 @@ extern "C" {
 #endif
 
 /* arc4.c:43-67 — KSA.  Only the first 256 key bytes matter; keylen 0 behaves
- * like the reference (key[0] repeated).  void: a GPU failure aborts loudly. */
+ * like the reference (key[0] repeated).  void: a GPU failure is
+ * reported on stderr and through bc_void_status() (bulkcipher.h); ctx is left untouched. */
 void arc4_setup(arc4_context *ctx, const unsigned char *key, unsigned int keylen);
 /* arc4.c:72-97 — PRGA into `keystream`; ctx->x, y, m persist.  Returns 0. */
 int arc4_prep(arc4_context *ctx, size_t length, unsigned char *keystream);

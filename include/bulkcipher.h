@@ -41,6 +41,12 @@ extern "C" {
 #define BC_DECRYPT 0                 /* == AES_DECRYPT, aes-modes/aes.h:34 */
 
 const char *bc_last_error(void);
+/* The reference's void entry points (aesni.h bulk calls, arc4_setup, rc4_init, rc4_crypt) cannot
+ * return a failure.  When one fails it prints the message to stderr, leaves its output untouched
+ * and records the BC_ERR_* code for the calling thread; bc_void_status() returns that code (0 if
+ * none) and clears it.  With BULKCIPHER_ABORT_ON_ERROR=1 in the environment a failure aborts the
+ * process instead.  (Extension: the reference has no error reporting at all) */
+int  bc_void_status(void);
 int  bc_device_count(void);
 /* Device used by the calling thread's *_host calls and allocations (default 0). */
 int  bc_set_device(int device);
@@ -71,7 +77,8 @@ int   bc_device_sync(void);
  * bytes 0..7 (_mm_add_epi64, aesni.c:139,143).  nbytes need not be a multiple of
  * 16 (the last block is used partially, like aes.c:879-895).  If
  * d_last_keystream != NULL it receives the 16-byte keystream block of the last
- * block touched (the reference's stream_block on return).  in == out allowed. */
+ * block touched (the reference's stream_block on return); it must be 16-byte
+ * aligned like the data buffers.  in == out allowed. */
 int bc_aes_ctr_dev(const uint32_t *rk, int nr, const unsigned char counter[16], int counter_bits,
                    uint64_t first_block, const void *d_in, void *d_out, size_t nbytes,
                    void *d_last_keystream, void *stream);
@@ -93,8 +100,10 @@ int bc_aes_ecb_be32_dev(const uint32_t *rk, int nr, int mode, const void *d_in, 
 /* CBC decrypt, parallel over blocks.  Replaces aes_crypt_cbc(AES_DECRYPT)
  * (aes-modes/aes.c:784-797).  iv (host, 16 bytes) is read only; the caller gets
  * the new iv as the last ciphertext block (aes.c:792).  in == out is allowed
- * and then uses a library-owned scratch buffer in HBM (16 bytes per 4 KiB of
- * input) to keep the chunk-boundary ciphertext blocks. */
+ * and then keeps the ciphertext block in front of every 4 KiB row-group in
+ * scratch (16 bytes per 4 KiB of input) that is allocated and freed in stream
+ * order from a library-owned memory pool: any number of streams and host
+ * threads may run such calls at once, and nothing synchronises the device. */
 int bc_aes_cbc_decrypt_dev(const uint32_t *rk, int nr, const unsigned char iv[16],
                            const void *d_in, void *d_out, size_t nbytes, void *stream);
 
@@ -105,7 +114,7 @@ int bc_aes_cbc_decrypt_dev(const uint32_t *rk, int nr, const unsigned char iv[16
  * owns a memory pool and has to account for every byte on the device, and
  * latency-sensitive paths where the device-wide synchronisation an allocation
  * or free can imply would stall unrelated streams.  bc_aes_cbc_decrypt_dev
- * grows a library-owned scratch buffer on demand; this entry point instead
+ * takes its scratch from a memory pool that grows on demand; this entry point instead
  * parks the per-4-KiB boundary blocks in a fixed 1 MiB array that is part of
  * the library image (each GPU that loads the library holds it until exit) and
  * calls no cudaMalloc / cudaFree or any other allocating routine.
@@ -115,7 +124,10 @@ int bc_aes_cbc_decrypt_dev(const uint32_t *rk, int nr, const unsigned char iv[16
  *     block of one piece (read it before the call) as the iv of the next.
  *   - The first call on each device looks up the array's device address
  *     (cudaGetSymbolAddress, with that device current); make that first call
- *     before starting any stream capture.
+ *     before starting any stream capture.  That first call (per device and
+ *     key size) is also where the CUDA runtime loads the kernel image and the
+ *     library sets the kernel's shared-memory attribute: treat it as a warm-up
+ *     and make it before the budgeted or latency-critical phase begins.
  *   - All calls on a device share the one array, whatever the stream: two
  *     calls whose kernels can overlap on the GPU race on it.  Order them (same
  *     stream, or an event) — calls that follow one another need no clearing,
@@ -187,12 +199,55 @@ int bc_arc4_batch_host(size_t n_streams, const void *keys, unsigned keylen, size
 int bc_xor_host(const void *a, const void *b, void *out, size_t nbytes);
 
 /* ---- multi-GPU (one host thread per GPU, no collective) ------------------ */
-/* AES-CTR over a host buffer sharded across n_gpus devices by contiguous block
- * ranges: GPU g encrypts blocks [g*B/G, (g+1)*B/G) with its
- * counter offset by the first block index; the last GPU takes the remainder.
- * Equivalent to one bc_aes_ctr_host call. */
+/* The reference's slice drivers with a device per slice instead of a core per slice
+ * (aes-modes/test.c:28-44 ECB, :194-206 AES-NI ECB, :273-285 CTR; test.c:44-58 RC4 XOR):
+ * HOST buffers are cut into equal contiguous ranges, GPU g of n_gpus (devices 0..n_gpus-1) takes
+ * range g, the last GPU takes the remainder (the rule of aes-modes/test.c:33-35).  Each shard is
+ * an ordinary bc_*_host call on its own device from its own host thread, bound to the CPUs of
+ * the GPU's NUMA node; nothing is exchanged between GPUs.  The result is identical
+ * to the single bc_*_host call with the same arguments.
+ *
+ * CTR: by 16-byte block ranges; shard g's counter starts at its first block index (the
+ * reference harness restarts the counter per slice, aes-modes/test.c:282 — a bug not kept). */
 int bc_aes_ctr_host_multi(int n_gpus, const uint32_t *rk, int nr, const unsigned char counter[16],
                           int counter_bits, const void *in, void *out, size_t nbytes);
+/* ECB: by block ranges (whole blocks only). */
+int bc_aes_ecb_host_multi(int n_gpus, const uint32_t *rk, int nr, int mode,
+                          const void *in, void *out, size_t nbytes);
+/* CBC / CFB128 decrypt: by block ranges; shard g > 0 takes its chaining block from the last
+ * ciphertext block of shard g-1 (aes.c:784-797), read from `in` before anything is written, so
+ * in == out is fine. */
+int bc_aes_cbc_decrypt_host_multi(int n_gpus, const uint32_t *rk, int nr, const unsigned char iv[16],
+                                  const void *in, void *out, size_t nbytes);
+int bc_aes_cfb128_decrypt_host_multi(int n_gpus, const uint32_t *rk, int nr, const unsigned char iv[16],
+                                     const void *in, void *out, size_t nbytes);
+/* Batched CBC / CFB128 encrypt: by message index (a single message is a serial chain and does
+ * not shard: replicas only). */
+int bc_aes_cbc_encrypt_batch_host_multi(int n_gpus, const uint32_t *rk, int nr, size_t n_msgs, size_t msg_len,
+                                        const void *ivs, void *ivs_out, const void *in, void *out);
+int bc_aes_cfb128_encrypt_batch_host_multi(int n_gpus, const uint32_t *rk, int nr, size_t n_msgs, size_t msg_len,
+                                           const void *ivs, void *ivs_out, const void *in, void *out);
+/* Batched RC4: by stream index (keys, data and contexts of stream s stay together). */
+int bc_arc4_batch_host_multi(int n_gpus, size_t n_streams, const void *keys, unsigned keylen, size_t length,
+                             const void *in, void *out, const void *ctx_in, void *ctx_out);
+
+/* Host-side locality helpers used by the calls above (and by one-process-per-GPU callers such as
+ * bench.py before they allocate pinned memory).  bc_device_numa_node: the NUMA node the GPU's PCIe
+ * slot reports in sysfs, or -1.  bc_bind_host_thread_to_device: restrict the calling thread to
+ * that node's CPUs (within its current affinity mask) and prefer the node for its next page
+ * allocations; a no-op on single-node boxes.  The reference pins nothing (pthread_create with
+ * default attributes, aes-modes/test.c:80). */
+int bc_device_numa_node(int device);
+int bc_bind_host_thread_to_device(int device);
+
+/* ---- synthetic input for the harness -------------------------------------- */
+/* Device counterpart of the reference harness's generator (srand(1337); msg[i] = rand() % 255,
+ * aes-modes/test.c:54-56, :354) for buffers too large to build on the host (BASELINE config 5,
+ * 256 GiB): little-endian 64-bit word k of d_out = mix64(seed + first_word + k), where
+ *   mix64(x): z = x + 0x9e3779b97f4a7c15; z = (z ^ z>>30) * 0xbf58476d1ce4e5b9;
+ *             z = (z ^ z>>27) * 0x94d049bb133111eb; return z ^ z>>31      (splitmix64 output)
+ * so the host can replay any window of the logical buffer.  d_out 16-byte aligned. */
+int bc_fill_splitmix64_dev(void *d_out, size_t nbytes, uint64_t seed, uint64_t first_word, void *stream);
 
 /* ---- key schedules as plain word arrays (what aes_setkey_enc/dec compute) ---- */
 /* FIPS-197 expansion on little-endian words (aes-modes/aes.c:469-539); returns nr (10/12/14) or 0. */

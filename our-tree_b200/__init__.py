@@ -37,6 +37,7 @@ DROPIN_SYMBOLS = [
     "CheckAESSupport", "AES_256_Key_Expansion", "AES_128_Key_Expansion", "AES_192_Key_Expansion",
     "AES_ECB_encrypt", "AES_ECB_decrypt", "AES_CTR_encrypt",
     "arc4_setup", "arc4_prep", "arc4_crypt", "arc4_self_test", "rc4_init", "rc4_crypt",
+    "KEY_256_ASSIST_1", "KEY_256_ASSIST_2",       # exported by the reference's aesni.o, not in its header (aesni.c:13-36)
 ]
 BC_SYMBOLS = [
     "bc_last_error", "bc_device_count", "bc_set_device", "bc_get_device", "bc_sm_count", "bc_shutdown",
@@ -49,6 +50,9 @@ BC_SYMBOLS = [
     "bc_aes_expand_key", "bc_aes_invert_key",
     "bc_aes_ctr_host", "bc_aes_ecb_host", "bc_aes_cbc_decrypt_host", "bc_aes_cbc_encrypt_batch_host",
     "bc_arc4_batch_host", "bc_xor_host", "bc_aes_ctr_host_multi",
+    "bc_aes_ecb_host_multi", "bc_aes_cbc_decrypt_host_multi", "bc_aes_cfb128_decrypt_host_multi",
+    "bc_aes_cbc_encrypt_batch_host_multi", "bc_aes_cfb128_encrypt_batch_host_multi", "bc_arc4_batch_host_multi",
+    "bc_device_numa_node", "bc_bind_host_thread_to_device", "bc_fill_splitmix64_dev", "bc_void_status",
 ]
 
 
@@ -112,6 +116,22 @@ def lib() -> C.CDLL:
     L.bc_arc4_batch_host.argtypes = [sz, vp, u32, sz, vp, vp, vp, vp]
     L.bc_xor_host.argtypes = [vp, vp, vp, sz]
     L.bc_aes_ctr_host_multi.argtypes = [i32, vp, i32, vp, i32, vp, vp, sz]
+    L.bc_aes_ecb_host_multi.argtypes = [i32, vp, i32, i32, vp, vp, sz]
+    L.bc_aes_cbc_decrypt_host_multi.argtypes = [i32, vp, i32, vp, vp, vp, sz]
+    L.bc_aes_cfb128_decrypt_host_multi.argtypes = [i32, vp, i32, vp, vp, vp, sz]
+    L.bc_aes_cbc_encrypt_batch_host_multi.argtypes = [i32, vp, i32, sz, sz, vp, vp, vp, vp]
+    L.bc_aes_cfb128_encrypt_batch_host_multi.argtypes = [i32, vp, i32, sz, sz, vp, vp, vp, vp]
+    L.bc_arc4_batch_host_multi.argtypes = [i32, sz, vp, u32, sz, vp, vp, vp, vp]
+    L.bc_device_numa_node.argtypes = [i32]
+    L.bc_bind_host_thread_to_device.argtypes = [i32]
+    L.bc_fill_splitmix64_dev.argtypes = [vp, sz, u64, u64, vp]
+    # every pointer-taking symbol gets argtypes (64-bit pointers must not be truncated)
+    L.bc_aes_ecb_be32_dev.argtypes = [vp, i32, i32, vp, vp, sz, vp]
+    L.bc_aes_ecb_be32_host.argtypes = [vp, i32, i32, vp, vp, sz]
+    L.bc_aes_expand_key.argtypes = [vp, u32, vp]
+    L.bc_aes_invert_key.argtypes = [vp, i32, vp]
+    L.bc_aes_invert_key.restype = None
+    L.bc_set_device.argtypes = [i32]
     L.aes_setkey_enc.argtypes = [vp, vp, u32]
     L.aes_setkey_dec.argtypes = [vp, vp, u32]
     L.aes_crypt_ecb.argtypes = [vp, i32, vp, vp]
@@ -331,3 +351,41 @@ def aes_ctr_host_multi(n_gpus: int, rk, nr: int, counter: bytes, data, counter_b
     r = _rk(rk)
     check(lib().bc_aes_ctr_host_multi(n_gpus, _ptr(r), nr, bytes(counter), counter_bits, _ptr(d), _ptr(o), d.size))
     return o
+
+
+def aes_ecb_host_multi(n_gpus: int, rk, nr: int, mode: int, data) -> np.ndarray:
+    d = _u8(data)
+    o = np.empty_like(d)
+    r = _rk(rk)
+    check(lib().bc_aes_ecb_host_multi(n_gpus, _ptr(r), nr, mode, _ptr(d), _ptr(o), d.size))
+    return o
+
+
+def aes_chained_decrypt_host_multi(n_gpus: int, rk, nr: int, iv: bytes, data, inplace: bool = False, cfb: bool = False):
+    d = np.array(_u8(data))
+    o = d if inplace else np.empty_like(d)
+    r = _rk(rk)
+    fn = lib().bc_aes_cfb128_decrypt_host_multi if cfb else lib().bc_aes_cbc_decrypt_host_multi
+    check(fn(n_gpus, _ptr(r), nr, bytes(iv), _ptr(d), _ptr(o), d.size))
+    return o
+
+
+def aes_chained_encrypt_batch_host_multi(n_gpus: int, rk, nr: int, ivs, data, msg_len: int, cfb: bool = False):
+    d = _u8(data)
+    o = np.empty_like(d)
+    iv = _u8(ivs)
+    ivo = np.empty_like(iv)
+    r = _rk(rk)
+    fn = lib().bc_aes_cfb128_encrypt_batch_host_multi if cfb else lib().bc_aes_cbc_encrypt_batch_host_multi
+    check(fn(n_gpus, _ptr(r), nr, d.size // msg_len if msg_len else 0, msg_len, _ptr(iv), _ptr(ivo), _ptr(d), _ptr(o)))
+    return o, ivo
+
+
+def arc4_batch_host_multi(n_gpus: int, keys, keylen: int, data, length: int, want_ctx: bool = False):
+    d, k = _u8(data), _u8(keys)
+    n = k.size // keylen
+    o = np.empty_like(d)
+    ctx = np.zeros(n * 264, np.uint8) if want_ctx else None
+    check(lib().bc_arc4_batch_host_multi(n_gpus, n, _ptr(k), keylen, length, _ptr(d) if d.size else None,
+                                         _ptr(o) if d.size else None, None, _ptr(ctx) if want_ctx else None))
+    return (o, ctx) if want_ctx else o

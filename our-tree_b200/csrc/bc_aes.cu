@@ -506,6 +506,9 @@ aes_blocks_kernel(const __grid_constant__ AesSched ks, const __grid_constant__ B
                 carry.y = __shfl_sync(0xffffffffu, c.y, 31);
                 carry.z = __shfl_sync(0xffffffffu, c.z, 31);
                 carry.w = __shfl_sync(0xffffffffu, c.w, 31);
+                /* lane L just read in[b-1], the block lane L-1 stores below: order every lane's
+                 * loads before any lane's store (a shuffle converges the warp but is no fence) */
+                __syncwarp();
             }
             State s;
             if (MODE == MODE_CFB_DEC) s = State{ prev.x, prev.y, prev.z, prev.w };   /* P_i = E(C_{i-1}) ^ C_i (aes.c:832-842) */
@@ -801,6 +804,10 @@ extern "C" int bc_aes_ctr_dev(const uint32_t *rk, int nr, const unsigned char co
         return BC_ERR_BAD_ARG;
     }
     if ((rc = check_overlap(d_in, d_out, nbytes))) return rc;
+    if ((uintptr_t)d_last_keystream & 15u) {
+        bc_set_error("d_last_keystream must be 16-byte aligned (it is written with one 128-bit store)");
+        return BC_ERR_BAD_ARG;
+    }
     if (nbytes == 0) return BC_OK;
 
     uint64_t hi = 0, lo = 0;
@@ -903,18 +910,24 @@ int chained_decrypt_dev(const uint32_t *rk, int nr, const unsigned char iv[16],
                ((uint32_t)iv[4 * i + 3] << 24);
     a.iv = make_uint4(w[0], w[1], w[2], w[3]);
     cudaStream_t st = (cudaStream_t)stream;
+    void *scratch = nullptr;
     if (d_in == d_out && a.n_groups > 1) {
         /* in place: the block in front of each group would be overwritten by a
-         * neighbouring warp — keep copies in library-owned scratch first */
-        void *scratch = nullptr;
-        if ((rc = bc_scratch_get((void *)st, a.n_groups * sizeof(uint4), &scratch))) return rc;
+         * neighbouring warp — keep copies in stream-ordered scratch first */
+        if ((rc = bc_stream_scratch_alloc((void *)st, a.n_groups * sizeof(uint4), &scratch))) return rc;
         const int tpb = 256;
         const unsigned blocks = (unsigned)((a.n_groups + tpb - 1) / tpb);
         cbc_save_boundaries_kernel<<<blocks, tpb, 0, st>>>(a.in, (uint4 *)scratch, a.n_groups);
-        BC_CUDA(cudaGetLastError(), "cbc_save_boundaries_kernel launch");
+        cudaError_t e = cudaGetLastError();
+        if (e != cudaSuccess) { bc_stream_scratch_free((void *)st, scratch); return bc_cuda_fail((int)e, "cbc_save_boundaries_kernel launch"); }
         a.boundary = (const uint4 *)scratch;
     }
-    return launch_blocks_nr<MODE>(nr, ks, a, st);
+    rc = launch_blocks_nr<MODE>(nr, ks, a, st);
+    if (scratch) {                                   /* freed in stream order: after the kernel that reads it */
+        const int rc2 = bc_stream_scratch_free((void *)st, scratch);
+        if (rc == BC_OK) rc = rc2;
+    }
+    return rc;
 }
 
 template <bool CFB>

@@ -16,10 +16,13 @@ void bc_set_error(const char *fmt, ...);
 int  bc_cuda_fail(int cuda_err, const char *what);
 /* Number of SMs of the current device (cached per device). */
 int  bc_cached_sm_count(void);
-/* Grow-only per-device scratch buffer in HBM, owned by the library; one buffer
- * per `key` (the stream the work is queued on), so calls on different streams
- * never share scratch. */
+/* Grow-only per-device scratch buffer in HBM, owned by the library; one buffer per `key`.
+ * For the host pipeline's own fixed keys only (called under the device lock). */
 int  bc_scratch_get(void *key, size_t bytes, void **d_ptr);
+/* Stream-ordered scratch from a library-owned memory pool: valid for the work enqueued on
+ * `stream` between the two calls.  Any number of streams / host threads, no device sync. */
+int  bc_stream_scratch_alloc(void *stream, size_t bytes, void **d_ptr);
+int  bc_stream_scratch_free(void *stream, void *d_ptr);
 
 #define BC_CUDA(call, what)                                        \
     do {                                                           \

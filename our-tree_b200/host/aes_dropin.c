@@ -23,6 +23,8 @@ static uint32_t sub_word(uint32_t w)
            ((uint32_t)SBOX[(w >> 16) & 0xFF] << 16) | ((uint32_t)SBOX[w >> 24] << 24);
 }
 
+uint32_t bc_aes_sub_word(uint32_t w) { return sub_word(w); }    /* for aesni_dropin.c's KEY_256_ASSIST_2 */
+
 /* InvMixColumns of one little-endian column word: what RT0..3[FSb[.]] yields at
  * aes-modes/aes.c:580-589. */
 static uint32_t inv_mix_column(uint32_t w)

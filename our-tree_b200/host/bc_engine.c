@@ -12,11 +12,14 @@
  *
  * There is no CPU fallback: if CUDA is unusable every entry point fails.
  */
+#define _GNU_SOURCE
 #include <pthread.h>
+#include <sched.h>
 #include <stdarg.h>
 #include <stdio.h>
 #include <stdlib.h>
 #include <string.h>
+#include <sys/syscall.h>
 #include <unistd.h>
 
 #include <cuda_runtime_api.h>
@@ -49,6 +52,8 @@ void bc_set_error(const char *fmt, ...)
     va_end(ap);
 }
 
+void bc_set_error_str(const char *msg) { bc_set_error("%s", msg); }
+
 int bc_cuda_fail(int cuda_err, const char *what)
 {
     bc_set_error("%s: %s (%s)", what, cudaGetErrorString((cudaError_t)cuda_err),
@@ -57,6 +62,27 @@ int bc_cuda_fail(int cuda_err, const char *what)
 }
 
 const char *bc_last_error(void) { return tls_error; }
+
+/* The reference's void entry points (aesni.h bulk calls, arc4_setup, rc4_*) have no way to
+ * return a failure.  They report it here instead: the message goes to stderr, the output buffer
+ * is left untouched, the code is kept per thread until read.  BULKCIPHER_ABORT_ON_ERROR=1 turns a
+ * failure into abort() for hosts that prefer a crash to a missed check. */
+static __thread int tls_void_status = 0;
+
+void bc_void_call_failed(int rc, const char *fn)
+{
+    tls_void_status = rc;
+    fprintf(stderr, "libbulkcipher: %s failed (%d): %s - output left untouched (no CPU fallback)\n", fn, rc, tls_error);
+    const char *e = getenv("BULKCIPHER_ABORT_ON_ERROR");
+    if (e && *e && *e != '0') abort();
+}
+
+int bc_void_status(void)
+{
+    const int rc = tls_void_status;
+    tls_void_status = 0;
+    return rc;
+}
 
 /* ---------------------------------------------------------- device state */
 
@@ -84,6 +110,7 @@ typedef struct {
     int        sm_count;
     bc_slot    slot[BC_MAX_SLOTS];
     bc_scratch scratch[BC_MAX_SCRATCH];
+    cudaMemPool_t pool;         /* stream-ordered scratch (bc_stream_scratch_alloc); NULL until first use */
     unsigned char *d_aux;       /* small device buffer: ivs, keys, contexts, last keystream */
     size_t     aux_cap;
     /* enqueue-ahead pipeline for pinned callers: one stream per stage, events chain the slots */
@@ -160,9 +187,10 @@ int bc_sm_count(void)
     return bc_cached_sm_count();
 }
 
-/* Scratch in HBM, grow-only, one buffer per stream key so calls on different
- * streams do not share it.  Calls that reuse a stream are ordered by the
- * stream itself. */
+/* Scratch in HBM, grow-only, one buffer per key.  Only the library's own host-pipeline calls use
+ * this table, with a fixed key each and under the device lock, so an entry is never shared by two
+ * calls in flight.  Per-stream scratch of the device entry points comes from
+ * bc_stream_scratch_alloc below (stream-ordered, any number of streams). */
 int bc_scratch_get(void *key, size_t bytes, void **d_ptr)
 {
     bc_dev *d = cur_dev_state(NULL);
@@ -173,9 +201,10 @@ int bc_scratch_get(void *key, size_t bytes, void **d_ptr)
         if (d->scratch[i].ptr && d->scratch[i].key == key) s = &d->scratch[i];
     for (int i = 0; i < BC_MAX_SCRATCH && !s; i++)
         if (!d->scratch[i].ptr) s = &d->scratch[i];
-    if (!s) {                                    /* table full: recycle entry 0 after draining the device */
-        cudaDeviceSynchronize();
-        s = &d->scratch[0];
+    if (!s) {
+        pthread_mutex_unlock(&d->scratch_lock);
+        bc_set_error("internal scratch table full (%d keys)", BC_MAX_SCRATCH);
+        return BC_ERR_TOO_LARGE;
     }
     int rc = BC_OK;
     if (s->cap < bytes) {
@@ -189,6 +218,49 @@ int bc_scratch_get(void *key, size_t bytes, void **d_ptr)
     *d_ptr = s->ptr;
     pthread_mutex_unlock(&d->scratch_lock);
     return rc;
+}
+
+/* Stream-ordered scratch for the device entry points (in-place CBC/CFB decrypt keeps one
+ * ciphertext block per 4 KiB row-group): allocated and freed IN STREAM ORDER from a library-owned
+ * memory pool, so the buffer belongs to exactly the kernels enqueued between the two calls —
+ * whatever the number of streams or host threads — and no call ever synchronises the device.
+ * The pool keeps freed memory (release threshold = max), so steady-state calls cost microseconds
+ * and touch the driver's allocator only when a larger buffer than ever before is needed. */
+int bc_stream_scratch_alloc(void *stream, size_t bytes, void **d_ptr)
+{
+    int dev = 0;
+    bc_dev *d = cur_dev_state(&dev);
+    if (!d) { bc_set_error("no current CUDA device"); return BC_ERR_NO_DEVICE; }
+    pthread_mutex_lock(&d->scratch_lock);
+    if (!d->pool) {
+        struct cudaMemPoolProps props;
+        memset(&props, 0, sizeof props);
+        props.allocType = cudaMemAllocationTypePinned;
+        props.handleTypes = cudaMemHandleTypeNone;
+        props.location.type = cudaMemLocationTypeDevice;
+        props.location.id = dev;
+        cudaError_t e = cudaMemPoolCreate(&d->pool, &props);
+        if (e == cudaSuccess) {
+            unsigned long long keep = ~0ull;
+            e = cudaMemPoolSetAttribute(d->pool, cudaMemPoolAttrReleaseThreshold, &keep);
+        }
+        if (e != cudaSuccess) {
+            if (d->pool) { cudaMemPoolDestroy(d->pool); d->pool = NULL; }
+            pthread_mutex_unlock(&d->scratch_lock);
+            return bc_cuda_fail((int)e, "cudaMemPoolCreate(scratch pool)");
+        }
+    }
+    cudaMemPool_t pool = d->pool;
+    pthread_mutex_unlock(&d->scratch_lock);
+    BC_CUDA(cudaMallocFromPoolAsync(d_ptr, bytes ? bytes : 16, pool, (cudaStream_t)stream), "cudaMallocFromPoolAsync(scratch)");
+    return BC_OK;
+}
+
+int bc_stream_scratch_free(void *stream, void *d_ptr)
+{
+    if (!d_ptr) return BC_OK;
+    BC_CUDA(cudaFreeAsync(d_ptr, (cudaStream_t)stream), "cudaFreeAsync(scratch)");
+    return BC_OK;
 }
 
 /* ----------------------------------------------------- memory conveniences */
@@ -485,6 +557,20 @@ static size_t pick_chunk(size_t nbytes, const void *in, const void *out)
     return c < cap ? c : cap;
 }
 
+/* The *_host calls take both buffers in host memory (staged pipeline) or both in device memory
+ * (launched in place, no staging).  One of each would have the pipeline dereference a device
+ * pointer on the CPU: refuse it instead of crashing. */
+static int check_same_side(const void *in, const void *out)
+{
+    const int ci = in ? classify(in) : -1, co = out ? classify(out) : -1;
+    if (ci >= 0 && co >= 0 && (ci == 2) != (co == 2)) {
+        bc_set_error("mixed buffers: `in` is %s memory but `out` is %s memory; pass both on the same side",
+                     ci == 2 ? "device" : "host", co == 2 ? "device" : "host");
+        return BC_ERR_BAD_ARG;
+    }
+    return BC_OK;
+}
+
 static int check_host_args(const uint32_t *rk, int nr, const void *in, const void *out, size_t nbytes)
 {
     if (!rk || (nr != 10 && nr != 12 && nr != 14)) {
@@ -492,7 +578,7 @@ static int check_host_args(const uint32_t *rk, int nr, const void *in, const voi
         return BC_ERR_BAD_ARG;
     }
     if (nbytes && (!in || !out)) { bc_set_error("NULL data pointer with nbytes=%zu", nbytes); return BC_ERR_BAD_ARG; }
-    return BC_OK;
+    return nbytes ? check_same_side(in, out) : BC_OK;
 }
 
 /* ------------------------------------------------------------- AES-CTR */
@@ -693,6 +779,10 @@ static int chained_encrypt_batch_host(int cfb, const uint32_t *rk, int nr, size_
     if (!ivs) { bc_set_error("ivs is NULL"); return BC_ERR_BAD_ARG; }
     bc_dev *d;
     if ((rc = dev_prepare(&d))) return rc;
+    if ((classify(in) == 2) != (classify(ivs) == 2) || (ivs_out && (classify(in) == 2) != (classify(ivs_out) == 2))) {
+        bc_set_error("mixed buffers: ivs / ivs_out must be on the same side (host or device) as the data");
+        return BC_ERR_BAD_ARG;
+    }
     if (classify(in) == 2 && classify(out) == 2 && classify(ivs) == 2) {
         rc = (cfb ? bc_aes_cfb128_encrypt_batch_dev : bc_aes_cbc_encrypt_batch_dev)(rk, nr, n_msgs, msg_len, ivs, ivs_out, in, out, NULL);
         return rc ? rc : bc_device_sync();
@@ -800,6 +890,20 @@ int bc_arc4_batch_host(size_t n_streams, const void *keys, unsigned keylen, size
     if (rc) return rc;
     if (!keylen) keylen = 1;
     const int with_ctx = (ctx_in || ctx_out);
+    {
+        /* all operands in device memory: launch in place, no staging; a mix is refused */
+        const void *ops[5] = { keys, in, out, ctx_in, ctx_out };
+        int n_dev = 0, n_host = 0;
+        for (int i = 0; i < 5; i++) if (ops[i]) { if (classify(ops[i]) == 2) n_dev++; else n_host++; }
+        if (n_dev && n_host) {
+            bc_set_error("mixed buffers: keys / data / contexts must all be host memory or all device memory");
+            return BC_ERR_BAD_ARG;
+        }
+        if (n_dev) {
+            rc = bc_arc4_batch_dev(n_streams, keys, keylen, length, in, out, ctx_in, ctx_out, NULL);
+            return rc ? rc : bc_device_sync();
+        }
+    }
     pthread_mutex_lock(&d->lock);
     if ((rc = dev_ensure_slots(d)) == BC_OK) {
         if (length <= BC_CHUNK_BYTES) {
@@ -892,6 +996,14 @@ int bc_xor_host(const void *a, const void *b, void *out, size_t nbytes)
     bc_dev *d;
     int rc = dev_prepare(&d);
     if (rc) return rc;
+    {
+        const int ca = classify(a) == 2, cb = classify(b) == 2, co = classify(out) == 2;
+        if (ca != cb || cb != co) {
+            bc_set_error("mixed buffers: a, b and out must all be host memory or all device memory");
+            return BC_ERR_BAD_ARG;
+        }
+        if (ca) { rc = bc_xor_dev(a, b, out, nbytes, NULL); return rc ? rc : bc_device_sync(); }
+    }
     pthread_mutex_lock(&d->lock);
     if ((rc = dev_ensure_slots(d)) == BC_OK) {
         void *d_b = NULL;
@@ -919,7 +1031,7 @@ int bc_shutdown(void)
     for (int dev = 0; dev < n && dev < BC_MAX_DEVICES; dev++) {
         bc_dev *d = &g_dev[dev];
         pthread_mutex_lock(&d->lock);
-        int touched = d->ready || d->d_aux;
+        int touched = d->ready || d->d_aux || d->pool;
         for (int i = 0; i < BC_MAX_SCRATCH; i++) touched |= d->scratch[i].ptr != NULL;
         if (touched && cudaSetDevice(dev) == cudaSuccess) {
             cudaError_t e = cudaDeviceSynchronize();
@@ -944,6 +1056,7 @@ int bc_shutdown(void)
             }
             if (d->d_aux) { cudaFree(d->d_aux); d->d_aux = NULL; d->aux_cap = 0; }
             pthread_mutex_lock(&d->scratch_lock);
+            if (d->pool) { cudaMemPoolDestroy(d->pool); d->pool = NULL; }
             for (int i = 0; i < BC_MAX_SCRATCH; i++)
                 if (d->scratch[i].ptr) { cudaFree(d->scratch[i].ptr); memset(&d->scratch[i], 0, sizeof d->scratch[i]); }
             pthread_mutex_unlock(&d->scratch_lock);
@@ -956,53 +1069,293 @@ int bc_shutdown(void)
 
 /* ------------------------------------------------------------ multi-GPU */
 
+/* Host-side locality: put the calling thread on the CPUs of the NUMA node the GPU hangs off and
+ * prefer that node for the pages it touches next (pinned staging buffers are allocated by the
+ * thread that first needs them).  On single-node boxes, or where sysfs does not say, this is a
+ * no-op.  Never fails the caller: locality is an optimisation, not a requirement. */
+
+static int parse_cpulist(const char *s, cpu_set_t *set)
+{
+    int n = 0;
+    CPU_ZERO(set);
+    while (*s) {
+        char *end;
+        long a = strtol(s, &end, 10), b = a;
+        if (end == s) break;
+        if (*end == '-') { s = end + 1; b = strtol(s, &end, 10); if (end == s) break; }
+        for (long c = a; c <= b && c < CPU_SETSIZE; c++) { CPU_SET((int)c, set); n++; }
+        s = (*end == ',') ? end + 1 : end;
+        if (*end != ',') break;
+    }
+    return n;
+}
+
+int bc_device_numa_node(int device)
+{
+    char bus[32] = { 0 }, path[128];
+    if (cudaDeviceGetPCIBusId(bus, (int)sizeof bus, device) != cudaSuccess) { cudaGetLastError(); return -1; }
+    for (char *c = bus; *c; c++) if (*c >= 'A' && *c <= 'Z') *c = (char)(*c - 'A' + 'a');
+    snprintf(path, sizeof path, "/sys/bus/pci/devices/%s/numa_node", bus);
+    FILE *f = fopen(path, "r");
+    if (!f) return -1;
+    int node = -1;
+    if (fscanf(f, "%d", &node) != 1) node = -1;
+    fclose(f);
+    return node;
+}
+
+int bc_bind_host_thread_to_device(int device)
+{
+    const int node = bc_device_numa_node(device);
+    if (node < 0) return BC_OK;
+    char path[128], buf[4096];
+    snprintf(path, sizeof path, "/sys/devices/system/node/node%d/cpulist", node);
+    FILE *f = fopen(path, "r");
+    if (!f) return BC_OK;
+    if (!fgets(buf, (int)sizeof buf, f)) { fclose(f); return BC_OK; }
+    fclose(f);
+    cpu_set_t want, have, both;
+    if (parse_cpulist(buf, &want) <= 0) return BC_OK;
+    if (sched_getaffinity(0, sizeof have, &have) != 0) return BC_OK;
+    CPU_AND(&both, &want, &have);
+    if (CPU_COUNT(&both) == 0) return BC_OK;              /* the node's CPUs are outside our cgroup: leave things be */
+    sched_setaffinity(0, sizeof both, &both);
+#ifdef SYS_set_mempolicy
+    if (node < 64) {
+        unsigned long mask = 1ul << node;
+        syscall(SYS_set_mempolicy, 1 /* MPOL_PREFERRED */, &mask, 65ul);
+    }
+#endif
+    return BC_OK;
+}
+
+/* One host thread per GPU: the reference's slice drivers (aes-modes/test.c:28-44,
+ * 194-206, 273-285; test.c:44-58) with a device per slice instead of a core per slice.  No
+ * collective: every shard is an ordinary bc_*_host call on its own device. */
+typedef enum { SH_CTR, SH_ECB, SH_CBC_DEC, SH_CFB_DEC, SH_CBC_ENC, SH_CFB_ENC, SH_RC4 } shard_kind;
+
 typedef struct {
-    int device; const uint32_t *rk; int nr; const unsigned char *counter; int bits;
-    uint64_t first_block; const unsigned char *in; unsigned char *out; size_t nbytes; int rc;
-    char err[256];
+    int device; shard_kind kind; int rc; char err[256];
+    const uint32_t *rk; int nr; int mode_or_bits;
+    const unsigned char *counter; uint64_t first_block;        /* CTR */
+    unsigned char iv[16];                                      /* chained decrypt: this shard's chaining block */
+    size_t n_items, item_len; unsigned keylen;                 /* batched ops: messages / streams */
+    const unsigned char *side_in; unsigned char *side_out;     /* ivs / keys in, ivs_out out */
+    const unsigned char *ctx_in; unsigned char *ctx_out;       /* RC4 contexts */
+    const unsigned char *in; unsigned char *out; size_t nbytes;
 } shard_job;
 
 static void *shard_main(void *p)
 {
     shard_job *j = (shard_job *)p;
     j->rc = bc_set_device(j->device);
-    if (j->rc == BC_OK)
-        j->rc = bc_aes_ctr_host(j->rk, j->nr, j->counter, j->bits, j->first_block, j->in, j->out, j->nbytes, NULL);
+    if (j->rc == BC_OK) {
+        bc_bind_host_thread_to_device(j->device);
+        switch (j->kind) {
+        case SH_CTR:
+            j->rc = bc_aes_ctr_host(j->rk, j->nr, j->counter, j->mode_or_bits, j->first_block, j->in, j->out, j->nbytes, NULL);
+            break;
+        case SH_ECB:
+            j->rc = bc_aes_ecb_host(j->rk, j->nr, j->mode_or_bits, j->in, j->out, j->nbytes);
+            break;
+        case SH_CBC_DEC:
+            j->rc = bc_aes_cbc_decrypt_host(j->rk, j->nr, j->iv, j->in, j->out, j->nbytes);
+            break;
+        case SH_CFB_DEC:
+            j->rc = bc_aes_cfb128_decrypt_host(j->rk, j->nr, j->iv, j->in, j->out, j->nbytes);
+            break;
+        case SH_CBC_ENC:
+            j->rc = bc_aes_cbc_encrypt_batch_host(j->rk, j->nr, j->n_items, j->item_len, j->side_in, j->side_out, j->in, j->out);
+            break;
+        case SH_CFB_ENC:
+            j->rc = bc_aes_cfb128_encrypt_batch_host(j->rk, j->nr, j->n_items, j->item_len, j->side_in, j->side_out, j->in, j->out);
+            break;
+        case SH_RC4:
+            j->rc = bc_arc4_batch_host(j->n_items, j->side_in, j->keylen, j->item_len, j->in, j->out, j->ctx_in, j->ctx_out);
+            break;
+        }
+    }
     if (j->rc != BC_OK) snprintf(j->err, sizeof j->err, "GPU %d: %s", j->device, bc_last_error());
     return NULL;
 }
 
-/* Equal contiguous block ranges, remainder to the last GPU (the reference's
- * slice rule, aes-modes/test.c:33-35, minus its bug of restarting the counter
- * on every slice, :273-285): shard g starts its counter at first block index. */
-int bc_aes_ctr_host_multi(int n_gpus, const uint32_t *rk, int nr, const unsigned char counter[16],
-                          int counter_bits, const void *in, void *out, size_t nbytes)
+static int shards_check(int n_gpus)
 {
     if (n_gpus < 1 || n_gpus > BC_MAX_DEVICES) { bc_set_error("n_gpus=%d out of range", n_gpus); return BC_ERR_BAD_ARG; }
     int have = bc_device_count();
     if (have < n_gpus) { bc_set_error("asked for %d GPUs, %d visible", n_gpus, have); return BC_ERR_NO_DEVICE; }
-    const size_t total_blocks = (nbytes + 15) / 16;
-    const size_t per = total_blocks / (size_t)n_gpus;
-    shard_job jobs[BC_MAX_DEVICES];
+    return BC_OK;
+}
+
+/* Run jobs[0..n) on devices 0..n-1, one thread each; shards with nothing to do are skipped. */
+static int shards_run(shard_job *jobs, int n)
+{
     pthread_t th[BC_MAX_DEVICES];
-    int started = 0, rc = BC_OK;
-    for (int g = 0; g < n_gpus; g++) {
-        const size_t b0 = per * (size_t)g;
-        const size_t byte0 = b0 * 16;
-        const size_t byte1 = (g == n_gpus - 1) ? nbytes : (b0 + per) * 16;
-        shard_job *j = &jobs[g];
-        j->device = g; j->rk = rk; j->nr = nr; j->counter = counter; j->bits = counter_bits;
-        j->first_block = b0;
-        j->in = (const unsigned char *)in + byte0;
-        j->out = (unsigned char *)out + byte0;
-        j->nbytes = byte1 > byte0 ? byte1 - byte0 : 0;
-        j->rc = BC_OK; j->err[0] = 0;
-        if (pthread_create(&th[g], NULL, shard_main, j) != 0) { bc_set_error("pthread_create failed"); rc = BC_ERR_BAD_ARG; break; }
-        started++;
+    int started[BC_MAX_DEVICES] = { 0 }, rc = BC_OK;
+    for (int g = 0; g < n; g++) {
+        jobs[g].device = g; jobs[g].rc = BC_OK; jobs[g].err[0] = 0;
+        const int empty = (jobs[g].kind == SH_CBC_ENC || jobs[g].kind == SH_CFB_ENC || jobs[g].kind == SH_RC4)
+                              ? jobs[g].n_items == 0 : jobs[g].nbytes == 0;
+        if (empty) continue;
+        if (pthread_create(&th[g], NULL, shard_main, &jobs[g]) != 0) { bc_set_error("pthread_create failed"); rc = BC_ERR_BAD_ARG; break; }
+        started[g] = 1;
     }
-    for (int g = 0; g < started; g++) {
+    for (int g = 0; g < n; g++) {
+        if (!started[g]) continue;
         pthread_join(th[g], NULL);
         if (jobs[g].rc != BC_OK && rc == BC_OK) { rc = jobs[g].rc; bc_set_error("%s", jobs[g].err); }
     }
     return rc;
+}
+
+/* Equal contiguous ranges of `total` items, remainder to the last GPU (the reference's slice
+ * rule, aes-modes/test.c:33-35). */
+static void shard_range(size_t total, int n, int g, size_t *first, size_t *count)
+{
+    const size_t per = total / (size_t)n;
+    *first = per * (size_t)g;
+    *count = (g == n - 1) ? total - *first : per;
+}
+
+/* CTR: unlike the reference harness, which restarts the counter on every slice
+ * (aes-modes/test.c:273-285), shard g starts its counter at its first block index. */
+int bc_aes_ctr_host_multi(int n_gpus, const uint32_t *rk, int nr, const unsigned char counter[16],
+                          int counter_bits, const void *in, void *out, size_t nbytes)
+{
+    int rc = shards_check(n_gpus);
+    if (rc) return rc;
+    shard_job jobs[BC_MAX_DEVICES];
+    memset(jobs, 0, sizeof jobs);
+    const size_t total_blocks = (nbytes + 15) / 16;
+    for (int g = 0; g < n_gpus; g++) {
+        size_t b0, nb;
+        shard_range(total_blocks, n_gpus, g, &b0, &nb);
+        const size_t byte0 = b0 * 16;
+        const size_t byte1 = (g == n_gpus - 1) ? nbytes : (b0 + nb) * 16;
+        shard_job *j = &jobs[g];
+        j->kind = SH_CTR; j->rk = rk; j->nr = nr; j->counter = counter; j->mode_or_bits = counter_bits;
+        j->first_block = b0;
+        j->in = (const unsigned char *)in + byte0;
+        j->out = (unsigned char *)out + byte0;
+        j->nbytes = byte1 > byte0 ? byte1 - byte0 : 0;
+    }
+    return shards_run(jobs, n_gpus);
+}
+
+/* ECB: whole blocks, contiguous block ranges (aes-modes/test.c:28-44, :194-206). */
+int bc_aes_ecb_host_multi(int n_gpus, const uint32_t *rk, int nr, int mode, const void *in, void *out, size_t nbytes)
+{
+    int rc = shards_check(n_gpus);
+    if (rc) return rc;
+    shard_job jobs[BC_MAX_DEVICES];
+    memset(jobs, 0, sizeof jobs);
+    for (int g = 0; g < n_gpus; g++) {
+        size_t b0, nb;
+        shard_range(nbytes / 16, n_gpus, g, &b0, &nb);
+        shard_job *j = &jobs[g];
+        j->kind = SH_ECB; j->rk = rk; j->nr = nr; j->mode_or_bits = mode;
+        j->in = (const unsigned char *)in + b0 * 16;
+        j->out = (unsigned char *)out + b0 * 16;
+        j->nbytes = nb * 16;
+    }
+    return shards_run(jobs, n_gpus);
+}
+
+/* CBC / CFB128 decrypt: shard g > 0 chains from the last ciphertext block of shard g-1
+ * (aes.c:784-797: P_i = D(C_i) ^ C_{i-1}), which is input data — read here, before any shard
+ * runs, because with in == out the neighbour's output would overwrite it. */
+static int chained_decrypt_host_multi(int cfb, int n_gpus, const uint32_t *rk, int nr, const unsigned char iv[16],
+                                      const void *in, void *out, size_t nbytes)
+{
+    int rc = shards_check(n_gpus);
+    if (rc) return rc;
+    if (!iv) { bc_set_error("iv is NULL"); return BC_ERR_BAD_ARG; }
+    if (nbytes % 16) { bc_set_error("%s length %zu is not a multiple of 16", cfb ? "CFB128" : "CBC", nbytes); return BC_ERR_BAD_ARG; }
+    if (nbytes && (!in || !out)) { bc_set_error("NULL data pointer with nbytes=%zu", nbytes); return BC_ERR_BAD_ARG; }
+    if (nbytes && (classify(in) == 2 || classify(out) == 2)) {
+        bc_set_error("the *_host_multi calls take HOST buffers (a device buffer lives on one GPU)");
+        return BC_ERR_BAD_ARG;
+    }
+    shard_job jobs[BC_MAX_DEVICES];
+    memset(jobs, 0, sizeof jobs);
+    for (int g = 0; g < n_gpus; g++) {
+        size_t b0, nb;
+        shard_range(nbytes / 16, n_gpus, g, &b0, &nb);
+        shard_job *j = &jobs[g];
+        j->kind = cfb ? SH_CFB_DEC : SH_CBC_DEC; j->rk = rk; j->nr = nr;
+        if (nb) memcpy(j->iv, b0 == 0 ? iv : (const unsigned char *)in + b0 * 16 - 16, 16);
+        j->in = (const unsigned char *)in + b0 * 16;
+        j->out = (unsigned char *)out + b0 * 16;
+        j->nbytes = nb * 16;
+    }
+    return shards_run(jobs, n_gpus);
+}
+
+int bc_aes_cbc_decrypt_host_multi(int n_gpus, const uint32_t *rk, int nr, const unsigned char iv[16],
+                                  const void *in, void *out, size_t nbytes)
+{
+    return chained_decrypt_host_multi(0, n_gpus, rk, nr, iv, in, out, nbytes);
+}
+
+int bc_aes_cfb128_decrypt_host_multi(int n_gpus, const uint32_t *rk, int nr, const unsigned char iv[16],
+                                     const void *in, void *out, size_t nbytes)
+{
+    return chained_decrypt_host_multi(1, n_gpus, rk, nr, iv, in, out, nbytes);
+}
+
+/* Batched CBC / CFB128 encrypt: by message index; a single message does not shard. */
+static int chained_encrypt_batch_host_multi(int cfb, int n_gpus, const uint32_t *rk, int nr, size_t n_msgs, size_t msg_len,
+                                            const void *ivs, void *ivs_out, const void *in, void *out)
+{
+    int rc = shards_check(n_gpus);
+    if (rc) return rc;
+    shard_job jobs[BC_MAX_DEVICES];
+    memset(jobs, 0, sizeof jobs);
+    for (int g = 0; g < n_gpus; g++) {
+        size_t m0, nm;
+        shard_range(n_msgs, n_gpus, g, &m0, &nm);
+        shard_job *j = &jobs[g];
+        j->kind = cfb ? SH_CFB_ENC : SH_CBC_ENC; j->rk = rk; j->nr = nr;
+        j->n_items = nm; j->item_len = msg_len;
+        j->side_in = ivs ? (const unsigned char *)ivs + 16 * m0 : NULL;
+        j->side_out = ivs_out ? (unsigned char *)ivs_out + 16 * m0 : NULL;
+        j->in = (const unsigned char *)in + m0 * msg_len;
+        j->out = (unsigned char *)out + m0 * msg_len;
+    }
+    return shards_run(jobs, n_gpus);
+}
+
+int bc_aes_cbc_encrypt_batch_host_multi(int n_gpus, const uint32_t *rk, int nr, size_t n_msgs, size_t msg_len,
+                                        const void *ivs, void *ivs_out, const void *in, void *out)
+{
+    return chained_encrypt_batch_host_multi(0, n_gpus, rk, nr, n_msgs, msg_len, ivs, ivs_out, in, out);
+}
+
+int bc_aes_cfb128_encrypt_batch_host_multi(int n_gpus, const uint32_t *rk, int nr, size_t n_msgs, size_t msg_len,
+                                           const void *ivs, void *ivs_out, const void *in, void *out)
+{
+    return chained_encrypt_batch_host_multi(1, n_gpus, rk, nr, n_msgs, msg_len, ivs, ivs_out, in, out);
+}
+
+/* Batched RC4: by stream index (test.c:44-58 slices ONE stream's XOR; whole streams are the unit
+ * here because a single RC4 stream is a serial chain). */
+int bc_arc4_batch_host_multi(int n_gpus, size_t n_streams, const void *keys, unsigned keylen, size_t length,
+                             const void *in, void *out, const void *ctx_in, void *ctx_out)
+{
+    int rc = shards_check(n_gpus);
+    if (rc) return rc;
+    shard_job jobs[BC_MAX_DEVICES];
+    memset(jobs, 0, sizeof jobs);
+    for (int g = 0; g < n_gpus; g++) {
+        size_t s0, ns;
+        shard_range(n_streams, n_gpus, g, &s0, &ns);
+        shard_job *j = &jobs[g];
+        j->kind = SH_RC4; j->n_items = ns; j->item_len = length; j->keylen = keylen;
+        j->side_in = keys ? (const unsigned char *)keys + s0 * keylen : NULL;
+        j->ctx_in = ctx_in ? (const unsigned char *)ctx_in + s0 * BC_ARC4_CTX_BYTES : NULL;
+        j->ctx_out = ctx_out ? (unsigned char *)ctx_out + s0 * BC_ARC4_CTX_BYTES : NULL;
+        j->in = in ? (const unsigned char *)in + s0 * length : NULL;
+        j->out = out ? (unsigned char *)out + s0 * length : NULL;
+    }
+    return shards_run(jobs, n_gpus);
 }

@@ -11,11 +11,14 @@
 #include "rc4.h"
 #include "bulkcipher.h"
 
+void bc_set_error_str(const char *msg);              /* bc_engine.c */
+void bc_void_call_failed(int rc, const char *fn);   /* bc_engine.c: stderr + bc_void_status(), abort only on request */
+
+/* The reference's calls are void: a failure is reported (stderr, bc_last_error(), bc_void_status())
+ * and the output buffer is left untouched — never garbage, never a silent CPU fallback. */
 static void die_on(int rc, const char *fn)
 {
-    if (rc == BC_OK) return;
-    fprintf(stderr, "libbulkcipher: %s failed (%d): %s — no CPU fallback, aborting\n", fn, rc, bc_last_error());
-    abort();
+    if (rc != BC_OK) bc_void_call_failed(rc, fn);
 }
 
 /* arc4.c:43-67 */
@@ -71,9 +74,14 @@ int arc4_self_test(int verbose)
 void rc4_init(struct rc4_state *const state, const char *key, int keylen)
 {
     arc4_context c;
-    if (keylen < 1) die_on(BC_ERR_BAD_ARG, "rc4_init (keylen must be >= 1; the reference divides by it, rc4.c:69)");
+    if (keylen < 1) {
+        bc_set_error_str("keylen must be >= 1 (the reference divides by it, rc4.c:69)");
+        die_on(BC_ERR_BAD_ARG, "rc4_init");
+        return;
+    }
     /* key[i % keylen] over 256 steps only ever reads the first 256 bytes */
-    die_on(bc_arc4_batch_host(1, key, (unsigned)(keylen > 256 ? 256 : keylen), 0, NULL, NULL, NULL, &c), "rc4_init");
+    const int rc = bc_arc4_batch_host(1, key, (unsigned)(keylen > 256 ? 256 : keylen), 0, NULL, NULL, NULL, &c);
+    if (rc != BC_OK) { die_on(rc, "rc4_init"); return; }         /* state left untouched */
     memcpy(state->perm, c.m, 256);
     state->index1 = 0;
     state->index2 = 0;
@@ -87,7 +95,8 @@ void rc4_crypt(struct rc4_state *const state, const char *inbuf, char *outbuf, i
     c.x = state->index1 & 0xFF;
     c.y = state->index2 & 0xFF;
     memcpy(c.m, state->perm, 256);
-    die_on(bc_arc4_batch_host(1, NULL, 0, (size_t)buflen, inbuf, outbuf, &c, &c), "rc4_crypt");
+    const int rc = bc_arc4_batch_host(1, NULL, 0, (size_t)buflen, inbuf, outbuf, &c, &c);
+    if (rc != BC_OK) { die_on(rc, "rc4_crypt"); return; }        /* state and output left untouched */
     memcpy(state->perm, c.m, 256);
     state->index1 = c.x;
     state->index2 = c.y;

@@ -32,7 +32,10 @@ def test_build_and_symbols(pkg):
     L = pkg.lib()
     declared = header_functions()
     assert len(declared) >= 40
-    assert set(pkg.DROPIN_SYMBOLS + pkg.BC_SYMBOLS) <= declared | {"bc_xor_dev", "bc_xor_host"}
+    # KEY_256_ASSIST_*: exported by the reference's aesni.o but absent from its header (aesni.c:13-36) — same here
+    assert set(pkg.DROPIN_SYMBOLS + pkg.BC_SYMBOLS) <= declared | {"bc_xor_dev", "bc_xor_host", "KEY_256_ASSIST_1", "KEY_256_ASSIST_2"}
+    for name in pkg.DROPIN_SYMBOLS + pkg.BC_SYMBOLS:
+        assert hasattr(L, name), f"libbulkcipher.so does not export {name}"
     for name in sorted(declared):
         assert hasattr(L, name), f"libbulkcipher.so does not export {name} declared in include/"
 
@@ -87,6 +90,34 @@ def test_error_codes_without_compute(pkg):
     assert L.bc_aes_ctr_dev(rk.ctypes.data, 10, bytes(16), 96, 0, None, None, 0, None, None) == pkg.BC_ERR_BAD_ARG
     assert L.bc_aes_cbc_decrypt_dev(rk.ctypes.data, 10, bytes(16), 16, 16, 24, None) == pkg.BC_ERR_BAD_ARG
     assert L.bc_aes_ecb_dev(rk.ctypes.data, 10, 1, 4096, 4096 + 32, 64, None) == pkg.BC_ERR_OVERLAP
+
+
+def test_key_256_assist_helpers_match_reference(pkg, ref):
+    """KEY_256_ASSIST_1/2 (aesni.c:13-36) against the unmodified reference object, and chained the way
+    AES_256_Key_Expansion chains them (aesni.c:38-77) they rebuild the schedule."""
+    L = pkg.lib()
+    rng = np.random.default_rng(41)
+    for _ in range(50):
+        a, b = rng.integers(0, 256, 16, dtype=np.uint8), rng.integers(0, 256, 16, dtype=np.uint8)
+        for name in ("KEY_256_ASSIST_1", "KEY_256_ASSIST_2"):
+            m1, m2, r1, r2 = a.copy(), b.copy(), a.copy(), b.copy()
+            getattr(L, name)(C.c_void_p(m1.ctypes.data), C.c_void_p(m2.ctypes.data))
+            getattr(ref.lib, "ref_" + name)(C.c_void_p(r1.ctypes.data), C.c_void_p(r2.ctypes.data))
+            assert np.array_equal(m1, r1) and np.array_equal(m2, r2), name
+
+
+def test_void_dropins_report_instead_of_aborting(pkg):
+    """A failing void entry point leaves its output untouched and parks the code in bc_void_status()."""
+    L = pkg.lib()
+    assert L.bc_void_status() == 0
+    src, dst = np.arange(32, dtype=np.uint8), np.full(32, 0xEE, np.uint8)
+    L.AES_ECB_encrypt(src.ctypes.data, dst.ctypes.data, 32, bytes(240), 11)          # 11 rounds: no such AES
+    assert L.bc_void_status() == pkg.BC_ERR_BAD_ARG and "rounds" in pkg.last_error()
+    assert (dst == 0xEE).all()
+    assert L.bc_void_status() == 0                                                    # cleared on read
+    st = pkg.rc4_state()
+    L.rc4_init(C.byref(st), b"k", 0)                                                  # rc4.c:69 would divide by zero
+    assert L.bc_void_status() == pkg.BC_ERR_BAD_ARG and not any(st.perm)
 
 
 def test_no_cpu_fallback(pkg):

@@ -65,6 +65,53 @@ def test_concurrent_streams_inplace_cbc(pkg, orc):
                 assert np.array_equal(G.host(b), orc.aes_cbc(key, DEC, iv, d)[1])
 
 
+def test_many_streams_inplace_cbc_stream_ordered_scratch(pkg, orc):
+    """In-place CBC decrypt on 20 streams at once, twice over: the boundary scratch is allocated and
+    freed in stream order (one buffer per call), so no count of streams makes two calls share one
+    (round 1 kept a table of 8 per-stream buffers and recycled entry 0 when it was full)."""
+    rng = np.random.default_rng(13)
+    L = pkg.lib()
+    key = rng.integers(0, 256, 16, dtype=np.uint8).tobytes()
+    rkd, nr = G.sched(pkg, key, DEC)
+    n = 20
+    streams = [torch.cuda.Stream() for _ in range(n)]
+    datas = [rng.integers(0, 256, (2 + i % 5) * (1 << 20) + 4096 * i, dtype=np.uint8) for i in range(n)]
+    ivs = [rng.integers(0, 256, 16, dtype=np.uint8).tobytes() for _ in range(n)]
+    wants = [orc.aes_cbc(key, DEC, iv, d)[1] for iv, d in zip(ivs, datas)]
+    for rep in range(2):
+        bufs = [G.to_dev(d) for d in datas]
+        torch.cuda.synchronize()
+        for s, b, iv, d in zip(streams, bufs, ivs, datas):
+            pkg.check(L.bc_aes_cbc_decrypt_dev(rkd.ctypes.data, nr, iv, b.data_ptr(), b.data_ptr(), d.size, s.cuda_stream))
+        torch.cuda.synchronize()
+        for b, w in zip(bufs, wants):
+            assert np.array_equal(G.host(b), w)
+
+
+def test_mixed_host_and_device_buffers_are_refused(pkg):
+    """One operand in HBM and the other in host memory: an error code, not a crash."""
+    L = pkg.lib()
+    rk, nr = G.sched(pkg, bytes(16), ENC)
+    d = G.to_dev(np.zeros(4096, np.uint8))
+    h = np.zeros(4096, np.uint8)
+    iv = bytes(16)
+    assert L.bc_aes_ctr_host(rk.ctypes.data, nr, iv, 128, 0, d.data_ptr(), h.ctypes.data, 4096, None) == pkg.BC_ERR_BAD_ARG
+    assert "mixed" in pkg.last_error()
+    assert L.bc_aes_ecb_host(rk.ctypes.data, nr, ENC, h.ctypes.data, d.data_ptr(), 4096) == pkg.BC_ERR_BAD_ARG
+    assert L.bc_aes_cbc_decrypt_host(rk.ctypes.data, nr, iv, d.data_ptr(), h.ctypes.data, 4096) == pkg.BC_ERR_BAD_ARG
+    assert L.bc_aes_cbc_encrypt_batch_host(rk.ctypes.data, nr, 1, 4096, h.ctypes.data, None, d.data_ptr(), d.data_ptr()) == pkg.BC_ERR_BAD_ARG
+    assert L.bc_xor_host(d.data_ptr(), h.ctypes.data, d.data_ptr(), 4096) == pkg.BC_ERR_BAD_ARG
+    assert L.bc_arc4_batch_host(1, h.ctypes.data, 16, 4096, d.data_ptr(), d.data_ptr(), None, None) == pkg.BC_ERR_BAD_ARG
+    # a misaligned last-keystream pointer is an argument error, not a sticky misaligned-address fault
+    ks = G.to_dev(np.zeros(64, np.uint8))
+    assert L.bc_aes_ctr_dev(rk.ctypes.data, nr, iv, 128, 0, d.data_ptr(), d.data_ptr(), 4096, ks.data_ptr() + 4, G.stream()) == pkg.BC_ERR_BAD_ARG
+    # all-device operands through the RC4 / XOR host calls are used in place
+    keys = G.to_dev(np.arange(16, dtype=np.uint8))
+    pkg.check(L.bc_arc4_batch_host(1, keys.data_ptr(), 16, 4096, d.data_ptr(), d.data_ptr(), None, None))
+    pkg.check(L.bc_xor_host(d.data_ptr(), d.data_ptr(), d.data_ptr(), 4096))
+    assert not G.host(d).any()
+
+
 def test_concurrent_host_threads(pkg, orc):
     """The reference harness calls the API from up to 8 pthreads on slices of one buffer with one shared
     key context (aes-modes/test.c:273-285): same here from Python threads (ctypes drops the GIL)."""

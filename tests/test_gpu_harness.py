@@ -44,15 +44,83 @@ def test_aes_gpu_cpp_facade():
     assert out.count("FIPS-197") == 3 and "Invalid AES key size" in out
 
 
-@pytest.mark.skipif(not os.environ.get("BULKCIPHER_RUN_REF_HARNESS"), reason="minutes-long; set BULKCIPHER_RUN_REF_HARNESS=1")
-def test_reference_harness_binaries_relinked():
-    """The reference's own aes-modes/test.c and test.c, compiled unmodified against include/ and linked
-    with libbulkcipher.so (`make ref-harness`): they must run to completion; test.c ends with the
-    reference's arc4_self_test, whose three 'passed' lines therefore come from the GPU path."""
-    aes, rc4 = os.path.join(BUILD, "ref_aes_modes_test"), os.path.join(BUILD, "ref_rc4_test")
-    if not (os.path.exists(aes) and os.path.exists(rc4)):
+def _need(*names):
+    paths = [os.path.join(BUILD, n) for n in names]
+    if not all(os.path.exists(p) for p in paths):
         pytest.skip("ref harness binaries not built (no reference tree where this was built)")
-    p = subprocess.run([aes], capture_output=True, text=True, timeout=1800)
-    assert p.returncode == 0 and "AESNI CTR, 1048576000, 8," in p.stdout, p.stdout[-2000:] + p.stderr[-2000:]
-    p = subprocess.run([rc4], capture_output=True, text=True, timeout=3000)
-    assert p.returncode == 0 and p.stdout.count("passed") == 3, p.stdout[-2000:] + p.stderr[-2000:]
+    return paths
+
+
+FULL = bool(os.environ.get("BULKCIPHER_RUN_REF_HARNESS"))     # let the reference's harnesses run to the end (minutes)
+
+
+def run_bounded(cmd, limit_s, log=None):
+    """Run a reference harness with line-buffered stdout under a time limit; returns (stdout, finished).
+    The reference's sweeps end in 1 GB cases that take minutes through pageable buffers / one serial
+    RC4 stream; the suite judges what was printed within the limit, a FULL run judges everything."""
+    try:
+        p = subprocess.run(["stdbuf", "-oL"] + cmd, capture_output=True, text=True, timeout=3000 if FULL else limit_s)
+        assert p.returncode == 0, p.stdout[-2000:] + p.stderr[-2000:]
+        out, done = p.stdout, True
+    except subprocess.TimeoutExpired as e:
+        out = e.stdout or ""
+        out, done = (out.decode(errors="replace") if isinstance(out, bytes) else out), False
+    if log:
+        os.makedirs(os.path.join(ROOT, "gpurun_out"), exist_ok=True)
+        with open(os.path.join(ROOT, "gpurun_out", log), "w") as f:
+            f.write(out + ("" if done else "\n[stopped by the test's time limit]\n"))
+    assert not (FULL and not done)
+    return out, done
+
+
+def test_reference_aes_harness_relinked():
+    """The reference's own aes-modes/test.c, compiled unmodified against THIS repo's include/ (make
+    ref-harness; build/ref_harness_includes.log lists the headers it saw) and linked with
+    libbulkcipher.so: `AESNI CTR` CSV lines with 10 timings each (aes-modes/test.c:287-350).  Its
+    buffers are malloc'ed (pageable) and its threads call AES_CTR_encrypt concurrently on slices."""
+    (aes,) = _need("ref_aes_modes_test")
+    out, done = run_bounded([aes], 60, "ref_aes_modes_test.log")
+    lines = [ln for ln in out.splitlines() if ln.startswith("AESNI CTR, ") and ln.rstrip().endswith(",")]
+    assert "## CPU Supports AES-NI instructions" in out                 # CheckAESSupport() = "GPU path usable"
+    for size in (1048576, 10485760, 104857600):
+        for t in (1, 2, 4, 8):
+            assert any(ln.startswith(f"AESNI CTR, {size}, {t}, ") for ln in lines), out[-1500:]
+    assert all(len([f for f in ln.split(",") if f.strip()]) == 13 for ln in lines), lines
+    if done:
+        assert len(lines) == 16 and "AESNI CTR, 1048576000, 8," in out
+
+
+def test_reference_rc4_harness_relinked():
+    """The reference's test.c the same way: every size up to 100 MB with all four thread counts within
+    the limit; a FULL run also reaches the reference's closing arc4_self_test (3 x passed, GPU path)."""
+    (rc4,) = _need("ref_rc4_test")
+    out, done = run_bounded([rc4], 75, "ref_rc4_test.log")
+    for size in (1048576, 10485760, 104857600):
+        for t in (1, 2, 4, 8):
+            assert f"RC4, {size}, {t}, " in out, out[-1500:]
+    assert out.count("Generated a new key in") >= 12
+    if done:
+        assert out.count("passed") == 3, out[-2000:]
+
+
+def test_reference_aes_gpu_mains_built_against_the_facade(orc):
+    """aes-gpu/Source/main_ecb_d.cu and main_ecb_e.cu, unmodified, as plain C++ over include/AES.h:
+    the decrypt CLI on FIPS-197 C.1-C.3 (words printed big-endian, %08X) and on a longer random
+    buffer against the oracle; the encrypt benchmark main prints its CSV lines."""
+    import numpy as np
+    dec, enc = _need("ref_aes_gpu_ecb_d", "ref_aes_gpu_ecb_e")
+    pt = "00112233445566778899AABBCCDDEEFF"
+    for key, ct in (("000102030405060708090A0B0C0D0E0F", "69C4E0D86A7B0430D8CDB78070B4C55A"),
+                    ("000102030405060708090A0B0C0D0E0F1011121314151617", "DDA97CA4864CDFE06EAF70A0EC0D7191"),
+                    ("000102030405060708090A0B0C0D0E0F101112131415161718191A1B1C1D1E1F", "8EA2B7CA516745BFEAFC49904B496089")):
+        assert run([dec, key, ct]).strip() == pt
+    rng = np.random.default_rng(3)
+    key = rng.integers(0, 256, 32, dtype=np.uint8).tobytes()
+    plain = rng.integers(0, 256, 16 * 100, dtype=np.uint8)
+    cipher = orc.aes_ecb(key, 1, plain)
+    assert run([dec, key.hex().upper(), cipher.tobytes().hex().upper()]).strip() == plain.tobytes().hex().upper()
+    assert "Invalid AES key size" in subprocess.run([dec, "0011", "00" * 16], capture_output=True, text=True).stdout
+    out, done = run_bounded([enc], 30, "ref_aes_gpu_ecb_e.log")
+    assert "AES ECB test, 1048576: " in out and "AES ECB test, 10485760: " in out and out.count("Average") >= 2
+    if done:
+        assert out.count("Average") == 4

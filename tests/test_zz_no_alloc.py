@@ -39,6 +39,7 @@ def test_no_alloc_matches_existing_entry_point_twice(pkg, orc):
     iv_a = rng.integers(0, 256, 16, dtype=np.uint8).tobytes()
     want_a, got_a = _both(pkg, rk, nr, iv_a, a)
     assert np.array_equal(got_a, want_a)
+    assert np.array_equal(got_a, orc.aes_cbc(key, DEC, iv_a, a)[1])       # the large case against the oracle too
     # call 2, straight after: other data, other key size, fewer groups — stale entries must not matter
     key2 = rng.integers(0, 256, 16, dtype=np.uint8).tobytes()
     rk2, nr2 = G.sched(pkg, key2, DEC)
@@ -51,6 +52,33 @@ def test_no_alloc_matches_existing_entry_point_twice(pkg, orc):
     c = rng.integers(0, 256, 16 * 9, dtype=np.uint8)
     want_c, got_c = _both(pkg, rk2, nr2, iv_b, c)
     assert np.array_equal(got_c, want_c)
+
+
+def test_no_alloc_leaves_free_device_memory_unchanged(pkg, orc):
+    """The reason the entry point exists: a caller whose HBM is fully budgeted must see exactly the
+    same free device memory before and after it.  The first call on a device (and per key size) is
+    a warm-up — it may load the kernel image and set its shared-memory attribute — so the check
+    brackets the calls that follow it."""
+    import torch
+
+    rng = np.random.default_rng(7)
+    key = rng.integers(0, 256, 16, dtype=np.uint8).tobytes()
+    rk, nr = G.sched(pkg, key, DEC)
+    data = rng.integers(0, 256, 64 * 1024 * 1024, dtype=np.uint8)         # 16384 row-groups
+    iv = bytes(range(16))
+    d = G.to_dev(data)
+    call = lambda: pkg.check(pkg.lib().bc_aes_cbc_decrypt_inplace_noalloc_dev(  # noqa: E731
+        rk.ctypes.data, nr, iv, d.data_ptr(), data.size, G.stream()))
+    call()                                                                # warm-up
+    torch.cuda.synchronize()
+    d.copy_(torch.from_numpy(data))                                       # restore the ciphertext (no new allocation)
+    torch.cuda.synchronize()
+    free_before, _ = torch.cuda.mem_get_info()
+    call()
+    torch.cuda.synchronize()
+    free_after, _ = torch.cuda.mem_get_info()
+    assert free_after == free_before, (free_before, free_after)
+    assert np.array_equal(G.host(d), orc.aes_cbc(key, DEC, iv, data)[1])
 
 
 def test_no_alloc_rejects_oversize(pkg):
