@@ -297,11 +297,12 @@ def run_reference(args):
 
 # ------------------------------------------------------------------------ our arm
 
-def link_probe(d_a, d_b):
-    """What the host link allows for an in+out transfer: 1 GiB H2D and 1 GiB D2H at the same time
-    (pinned memory, monolithic copies), GB/s per direction.  The e2e figure cannot exceed it.
-    Under torchrun every rank runs this at the same moment (the caller puts a barrier in front),
-    so the figure is what the box gives each GPU when all N links are busy at once."""
+def link_probe(d_a, d_b, ranks, n_gpus: int):
+    """What the host links allow for an in+out transfer: every rank copies 1 GiB H2D and 1 GiB D2H at
+    the same time (pinned memory, monolithic copies on two streams).  Each trial starts behind a
+    barrier on all N ranks and is timed as the MAX over ranks, so the figure is what the box gives
+    when all N links are busy for the whole trial: aggregate GB/s per direction = N GiB / slowest
+    rank's time.  The e2e figure cannot exceed it.  Returns (aggregate, slowest rank's own rate)."""
     import torch
 
     n = min(GIB, d_a.numel())
@@ -311,8 +312,8 @@ def link_probe(d_a, d_b):
     h_b.fill_(5)
     s1, s2 = torch.cuda.Stream(), torch.cuda.Stream()
     best = 1e9
-    for _ in range(3):
-        torch.cuda.synchronize()
+    for _ in range(4):
+        ranks.barrier()
         e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
         e0.record()
         s1.wait_event(e0)
@@ -325,8 +326,8 @@ def link_probe(d_a, d_b):
         torch.cuda.current_stream().wait_stream(s2)
         e1.record()
         torch.cuda.synchronize()
-        best = min(best, e0.elapsed_time(e1))
-    return n / best / 1e6
+        best = min(best, ranks.reduce([e0.elapsed_time(e1)], "max")[0])
+    return n_gpus * n / best / 1e6, n / best / 1e6
 
 
 class Ranks:
@@ -654,9 +655,8 @@ def run_ours(args):
     link = None
     if not in_place:
         try:
-            barrier()
-            mine = link_probe(d_in, d_out)
-            link = {"min": ranks.reduce([mine], "min")[0], "sum": ranks.reduce([mine], "sum")[0]}
+            agg, each = link_probe(d_in, d_out, ranks, n_gpus)
+            link = {"min": each, "sum": agg}
         except Exception as e:  # noqa: BLE001
             link = {"error": str(e)}
 
