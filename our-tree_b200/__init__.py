@@ -132,6 +132,7 @@ def lib() -> C.CDLL:
     L.bc_aes_invert_key.argtypes = [vp, i32, vp]
     L.bc_aes_invert_key.restype = None
     L.bc_set_device.argtypes = [i32]
+    L.bc_internal_reg_stats.argtypes = [vp]
     L.aes_setkey_enc.argtypes = [vp, vp, u32]
     L.aes_setkey_dec.argtypes = [vp, vp, u32]
     L.aes_crypt_ecb.argtypes = [vp, i32, vp, vp]

@@ -454,6 +454,228 @@ static int classify(const void *p)
     return 0;
 }
 
+/* ------------------------------------------- registration cache for pageable callers */
+
+/* The reference's harnesses malloc() their buffers once per test and hand the same ranges to the
+ * API ten times (aes-modes/test.c:287-350, test.c:60-125).  Pageable memory has to be staged through
+ * pinned buffers by host memcpy (about 20 GB/s); pinned memory is DMA'd directly (about 47 GB/s).
+ * So a large range that is seen a SECOND time is pinned in place (cudaHostRegister) and kept in a
+ * small LRU table; later calls on it take the pinned path.
+ *
+ * The danger of keeping a registration is a caller that frees the buffer and gets the same
+ * addresses back from a later malloc: the stale registration would still point at the OLD physical
+ * pages.  Nothing is assumed about that: the physical frame number of every page of the range is
+ * recorded at registration (from /proc/self/pagemap) and compared again before each use — pinned
+ * pages cannot move, so any difference means the range was unmapped or remapped; the entry is then
+ * dropped and the call is staged.  The kernel shows frame numbers only to privileged processes
+ * (CAP_SYS_ADMIN); where it does not, the cache stays off and pageable callers are staged as before.
+ * BULKCIPHER_REGISTER_PAGEABLE=0 turns it off, BULKCIPHER_REGISTER_MIN_MIB (default 64) sets the
+ * smallest range worth pinning, BULKCIPHER_REGISTER_MAX_GIB (default 16) caps the pinned total. */
+#include <fcntl.h>
+
+#define BC_REG_SLOTS 40
+typedef struct {
+    uintptr_t lo, hi;          /* byte range [lo, hi) exactly as the caller passed it */
+    int state;                 /* 0 free, 1 seen once, 2 registered, 3 registration refused (do not retry) */
+    int users;                 /* calls in flight that rely on the registration */
+    uint64_t tick;
+    uint64_t *pfn;             /* frame number per page of [page(lo), page(hi-1)] at registration */
+    size_t npages;
+} bc_reg;
+
+static bc_reg g_reg[BC_REG_SLOTS];
+static pthread_mutex_t g_reg_mu = PTHREAD_MUTEX_INITIALIZER;
+static uint64_t g_reg_tick;
+static int g_reg_mode = -1;        /* -1 unknown, 0 off, 1 on (frame numbers readable) */
+static int g_reg_fd = -1;
+static size_t g_reg_min = (size_t)64 << 20, g_reg_cap = (size_t)16 << 30, g_reg_total;
+static long g_page = 4096;
+static uint64_t g_reg_stats[4];    /* registrations, hits, stale drops, evictions (bc_internal_reg_stats) */
+
+#define PFN_MASK ((1ull << 55) - 1)
+
+static int read_pfns(uintptr_t lo, size_t npages, uint64_t *out)
+{
+    const off_t off = (off_t)(lo / (uintptr_t)g_page) * 8;
+    size_t got = 0;
+    while (got < npages * 8) {
+        ssize_t r = pread(g_reg_fd, (char *)out + got, npages * 8 - got, off + (off_t)got);
+        if (r <= 0) return -1;
+        got += (size_t)r;
+    }
+    for (size_t i = 0; i < npages; i++) {
+        if (!(out[i] >> 63)) return -1;                  /* page not present */
+        out[i] &= PFN_MASK;
+        if (!out[i]) return -1;                          /* frame number hidden */
+    }
+    return 0;
+}
+
+static void reg_init(void)
+{
+    g_reg_mode = 0;
+    const char *e = getenv("BULKCIPHER_REGISTER_PAGEABLE");
+    if (e && *e == '0') return;
+    e = getenv("BULKCIPHER_REGISTER_MIN_MIB");
+    if (e && atol(e) >= 1) g_reg_min = (size_t)atol(e) << 20;
+    e = getenv("BULKCIPHER_REGISTER_MAX_GIB");
+    if (e && atol(e) >= 1) g_reg_cap = (size_t)atol(e) << 30;
+    g_page = sysconf(_SC_PAGESIZE);
+    if (g_page <= 0) return;
+    g_reg_fd = open("/proc/self/pagemap", O_RDONLY | O_CLOEXEC);
+    if (g_reg_fd < 0) return;
+    volatile char probe = 1;                             /* a touched page of our own stack */
+    uint64_t v;
+    if (read_pfns((uintptr_t)&probe, 1, &v) != 0) { close(g_reg_fd); g_reg_fd = -1; return; }
+    (void)probe;
+    g_reg_mode = 1;
+}
+
+/* called with g_reg_mu held; the entry must have no users */
+static void reg_drop(bc_reg *r)
+{
+    if (r->state == 2) {
+        cudaError_t e = cudaHostUnregister((void *)r->lo);
+        if (e != cudaSuccess) cudaGetLastError();        /* the range may be gone already: nothing to undo */
+        g_reg_total -= r->hi - r->lo;
+    }
+    free(r->pfn);
+    memset(r, 0, sizeof *r);
+}
+
+/* Returns 1 when [p, p+n) may be DMA'd directly (a reference is then held until reg_release). */
+static int reg_acquire(const void *p, size_t n, int pageable)
+{
+    if (!p || n == 0) return 0;
+    pthread_mutex_lock(&g_reg_mu);
+    if (g_reg_mode < 0) reg_init();
+    if (g_reg_mode == 0) { pthread_mutex_unlock(&g_reg_mu); return 0; }
+    const uintptr_t lo = (uintptr_t)p, hi = lo + n;
+    /* A range that straddles one of our registrations (overlaps without lying inside it) would look
+     * pinned at one end and pageable at the other: retire that registration first. */
+    for (int i = 0; i < BC_REG_SLOTS; i++) {
+        bc_reg *r = &g_reg[i];
+        if (r->state == 2 && r->users == 0 && r->lo < hi && lo < r->hi && !(r->lo <= lo && hi <= r->hi)) reg_drop(r);
+    }
+    const uintptr_t plo = lo & ~((uintptr_t)g_page - 1);
+    const size_t npages = (size_t)((hi - 1 - plo) / (uintptr_t)g_page) + 1;
+    bc_reg *hit = NULL, *same = NULL, *freeslot = NULL, *lru = NULL;
+    for (int i = 0; i < BC_REG_SLOTS; i++) {
+        bc_reg *r = &g_reg[i];
+        if (r->state == 0) { if (!freeslot) freeslot = r; continue; }
+        if (r->state == 2 && r->lo <= lo && hi <= r->hi) hit = r;
+        if (r->lo == lo && r->hi == hi) same = r;
+        if (r->users == 0 && (!lru || r->tick < lru->tick)) lru = r;
+    }
+    int ok = 0;
+    /* memory we did not pin ourselves (the caller's own cudaHostAlloc / cudaHostRegister) or too small to be worth it */
+    if (!hit && (!pageable || n < g_reg_min)) { pthread_mutex_unlock(&g_reg_mu); return 0; }
+    uint64_t *now = (uint64_t *)malloc(npages * 8);
+    if (!now) { pthread_mutex_unlock(&g_reg_mu); return 0; }
+    if (hit) {
+        /* still the same physical pages as when it was pinned? */
+        const size_t first = (size_t)((plo - (hit->lo & ~((uintptr_t)g_page - 1))) / (uintptr_t)g_page);
+        if (read_pfns(plo, npages, now) == 0 && memcmp(now, hit->pfn + first, npages * 8) == 0) {
+            hit->users++; hit->tick = ++g_reg_tick; g_reg_stats[1]++; ok = 1;
+        } else if (hit->users == 0) {
+            g_reg_stats[2]++;
+            reg_drop(hit);                               /* freed and reused addresses: forget it, stage this call */
+        }
+    } else if (same && same->state == 1) {
+        /* second sighting: pin it.  Ranges that overlap it without containing it must go first. */
+        int blocked = 0;
+        for (int i = 0; i < BC_REG_SLOTS; i++) {
+            bc_reg *r = &g_reg[i];
+            if (r->state == 2 && r->lo < hi && lo < r->hi) { if (r->users) blocked = 1; else reg_drop(r); }
+        }
+        while (!blocked && g_reg_total + n > g_reg_cap) {
+            bc_reg *v = NULL;
+            for (int i = 0; i < BC_REG_SLOTS; i++)
+                if (g_reg[i].state == 2 && g_reg[i].users == 0 && (!v || g_reg[i].tick < v->tick)) v = &g_reg[i];
+            if (!v) { blocked = 1; break; }
+            g_reg_stats[3]++;
+            reg_drop(v);
+        }
+        if (!blocked) {
+            cudaError_t e = cudaHostRegister((void *)lo, n, cudaHostRegisterPortable);
+            if (e == cudaSuccess && read_pfns(plo, npages, now) == 0) {
+                same->state = 2; same->pfn = now; same->npages = npages; now = NULL;
+                same->users = 1; same->tick = ++g_reg_tick; g_reg_total += n; g_reg_stats[0]++; ok = 1;
+            } else {
+                if (e == cudaSuccess) cudaHostUnregister((void *)lo); else cudaGetLastError();
+                same->state = 3;
+            }
+        }
+    } else if (!same) {
+        bc_reg *r = freeslot;
+        if (!r && lru) { if (lru->state == 2) g_reg_stats[3]++; reg_drop(lru); r = lru; }
+        if (r) { r->lo = lo; r->hi = hi; r->state = 1; r->tick = ++g_reg_tick; }
+    } else {
+        same->tick = ++g_reg_tick;
+    }
+    free(now);
+    pthread_mutex_unlock(&g_reg_mu);
+    return ok;
+}
+
+static void reg_release(const void *p, size_t n)
+{
+    const uintptr_t lo = (uintptr_t)p, hi = lo + n;
+    pthread_mutex_lock(&g_reg_mu);
+    for (int i = 0; i < BC_REG_SLOTS; i++) {
+        bc_reg *r = &g_reg[i];
+        if (r->state == 2 && r->users > 0 && r->lo <= lo && hi <= r->hi) { r->users--; break; }
+    }
+    pthread_mutex_unlock(&g_reg_mu);
+}
+
+static void reg_shutdown(void)
+{
+    pthread_mutex_lock(&g_reg_mu);
+    for (int i = 0; i < BC_REG_SLOTS; i++) if (g_reg[i].state && g_reg[i].users == 0) reg_drop(&g_reg[i]);
+    pthread_mutex_unlock(&g_reg_mu);
+}
+
+/* test hook: registrations, hits, stale drops, evictions so far; returns 1 if the cache is active */
+int bc_internal_reg_stats(uint64_t out[4])
+{
+    pthread_mutex_lock(&g_reg_mu);
+    if (g_reg_mode < 0) reg_init();
+    memcpy(out, g_reg_stats, sizeof g_reg_stats);
+    const int on = g_reg_mode;
+    pthread_mutex_unlock(&g_reg_mu);
+    return on;
+}
+
+/* The pageable operands of one host call: pin the ones seen before, remember which to release. */
+#define BC_HOLD_MAX 6
+typedef struct { const void *p[BC_HOLD_MAX]; size_t n[BC_HOLD_MAX]; int held[BC_HOLD_MAX]; int count; } reg_hold;
+
+static void hold_add(reg_hold *h, const void *p, size_t n)
+{
+    if (!p || !n || h->count >= BC_HOLD_MAX) return;
+    for (int k = 0; k < h->count; k++) if (h->p[k] == p && h->n[k] == n) return;      /* in == out */
+    const int i = h->count++;
+    h->p[i] = p; h->n[i] = n; h->held[i] = 0;
+    /* every host range goes through the cache: one of OUR registrations is re-validated before each
+     * use (it would classify as pinned even after the caller freed and re-mapped the addresses) */
+    const int c = classify(p);
+    if (c != 2) h->held[i] = reg_acquire(p, n, c == 0);
+}
+
+static void hold_begin(reg_hold *h, const void *a, size_t na, const void *b, size_t nb, const void *c, size_t nc)
+{
+    h->count = 0;
+    hold_add(h, a, na);
+    hold_add(h, b, nb);
+    hold_add(h, c, nc);
+}
+
+static void hold_end(reg_hold *h)
+{
+    for (int i = 0; i < h->count; i++) if (h->held[i]) reg_release(h->p[i], h->n[i]);
+}
+
 /* wait for a slot's previous chunk and finish its staged copy-out */
 static int slot_retire(bc_slot *s)
 {
@@ -615,6 +837,8 @@ int bc_aes_ctr_host(const uint32_t *rk, int nr, const unsigned char counter[16],
         pthread_mutex_unlock(&d->lock);
         return rc;
     }
+    reg_hold h;
+    hold_begin(&h, in, nbytes, out, nbytes, NULL, 0);
     pthread_mutex_lock(&d->lock);
     if ((rc = dev_ensure_slots(d)) == BC_OK && (rc = dev_ensure_aux(d, 16)) == BC_OK) {
         ctr_op o = { rk, nr, counter, counter_bits, first_block, nbytes, last_keystream ? d->d_aux : NULL };
@@ -622,6 +846,7 @@ int bc_aes_ctr_host(const uint32_t *rk, int nr, const unsigned char counter[16],
         if (rc == BC_OK && last_keystream) rc = bc_memcpy_d2h(last_keystream, d->d_aux, 16);
     }
     pthread_mutex_unlock(&d->lock);
+    hold_end(&h);
     return rc;
 }
 
@@ -648,12 +873,15 @@ static int ecb_host(int be32, const uint32_t *rk, int nr, int mode, const void *
         rc = (be32 ? bc_aes_ecb_be32_dev : bc_aes_ecb_dev)(rk, nr, mode, in, out, nbytes, NULL);
         return rc ? rc : bc_device_sync();
     }
+    reg_hold h;
+    hold_begin(&h, in, nbytes, out, nbytes, NULL, 0);
     pthread_mutex_lock(&d->lock);
     if ((rc = dev_ensure_slots(d)) == BC_OK) {
         ecb_op o = { rk, nr, mode, be32 };
         rc = run_pipeline(d, (const unsigned char *)in, (unsigned char *)out, nbytes, pick_chunk(nbytes, in, out), ecb_chunk, &o);
     }
     pthread_mutex_unlock(&d->lock);
+    hold_end(&h);
     return rc;
 }
 
@@ -694,10 +922,12 @@ static int chained_decrypt_host(int cfb, const uint32_t *rk, int nr, const unsig
     }
     /* Chunk k chains from the last ciphertext block of chunk k-1.  Collect those
      * blocks first: with in == out the pipeline's D2H would overwrite them. */
+    reg_hold h;
+    hold_begin(&h, in, nbytes, out, nbytes, NULL, 0);
     const size_t chunk = pick_chunk(nbytes, in, out);
     const size_t n_chunks = (nbytes + chunk - 1) / chunk;
     unsigned char *ivs = (unsigned char *)malloc(16 * n_chunks);
-    if (!ivs) { bc_set_error("out of host memory"); return BC_ERR_BAD_ARG; }
+    if (!ivs) { hold_end(&h); bc_set_error("out of host memory"); return BC_ERR_BAD_ARG; }
     memcpy(ivs, iv, 16);
     for (size_t k = 1; k < n_chunks; k++) memcpy(ivs + 16 * k, (const unsigned char *)in + k * chunk - 16, 16);
     pthread_mutex_lock(&d->lock);
@@ -707,6 +937,7 @@ static int chained_decrypt_host(int cfb, const uint32_t *rk, int nr, const unsig
     }
     pthread_mutex_unlock(&d->lock);
     free(ivs);
+    hold_end(&h);
     return rc;
 }
 
@@ -787,6 +1018,9 @@ static int chained_encrypt_batch_host(int cfb, const uint32_t *rk, int nr, size_
         rc = (cfb ? bc_aes_cfb128_encrypt_batch_dev : bc_aes_cbc_encrypt_batch_dev)(rk, nr, n_msgs, msg_len, ivs, ivs_out, in, out, NULL);
         return rc ? rc : bc_device_sync();
     }
+    reg_hold h;
+    hold_begin(&h, in, n_msgs * msg_len, out, n_msgs * msg_len, ivs, 16 * n_msgs);
+    hold_add(&h, ivs_out, 16 * n_msgs);
     pthread_mutex_lock(&d->lock);
     if ((rc = dev_ensure_slots(d)) == BC_OK) {
         if (msg_len <= BC_CHUNK_BYTES) {
@@ -818,6 +1052,7 @@ static int chained_encrypt_batch_host(int cfb, const uint32_t *rk, int nr, size_
         }
     }
     pthread_mutex_unlock(&d->lock);
+    hold_end(&h);
     return rc;
 }
 
@@ -904,6 +1139,10 @@ int bc_arc4_batch_host(size_t n_streams, const void *keys, unsigned keylen, size
             return rc ? rc : bc_device_sync();
         }
     }
+    reg_hold h;
+    hold_begin(&h, in, n_streams * length, out, n_streams * length, keys, n_streams * (size_t)keylen);
+    hold_add(&h, ctx_in, n_streams * BC_ARC4_CTX_BYTES);
+    hold_add(&h, ctx_out, n_streams * BC_ARC4_CTX_BYTES);
     pthread_mutex_lock(&d->lock);
     if ((rc = dev_ensure_slots(d)) == BC_OK) {
         if (length <= BC_CHUNK_BYTES) {
@@ -962,6 +1201,7 @@ int bc_arc4_batch_host(size_t n_streams, const void *keys, unsigned keylen, size
     }
 rc4_done:
     pthread_mutex_unlock(&d->lock);
+    hold_end(&h);
     return rc;
 }
 
@@ -1004,6 +1244,8 @@ int bc_xor_host(const void *a, const void *b, void *out, size_t nbytes)
         }
         if (ca) { rc = bc_xor_dev(a, b, out, nbytes, NULL); return rc ? rc : bc_device_sync(); }
     }
+    reg_hold h;
+    hold_begin(&h, a, nbytes, b, nbytes, out, nbytes);
     pthread_mutex_lock(&d->lock);
     if ((rc = dev_ensure_slots(d)) == BC_OK) {
         void *d_b = NULL;
@@ -1013,6 +1255,7 @@ int bc_xor_host(const void *a, const void *b, void *out, size_t nbytes)
         }
     }
     pthread_mutex_unlock(&d->lock);
+    hold_end(&h);
     return rc;
 }
 
@@ -1063,6 +1306,7 @@ int bc_shutdown(void)
         }
         pthread_mutex_unlock(&d->lock);
     }
+    reg_shutdown();
     if (prev >= 0) cudaSetDevice(prev);
     return rc;
 }

@@ -136,3 +136,98 @@ def test_rc4_host_shapes(pkg, orc):
     assert np.array_equal(pkg.arc4_crypt(big, ks), want) and (c.x, c.y, bytes(c.m)) == (x, y, m)
     st = pkg.rc4_init(key)
     assert np.array_equal(pkg.rc4_crypt(st, big), want)
+
+
+# ---- pageable buffers that come back: the registration cache (host/bc_engine.c) ----
+
+def _reg_stats(pkg):
+    out = (ctypes.c_uint64 * 4)()
+    on = pkg.lib().bc_internal_reg_stats(out)
+    return on, list(out)
+
+
+class Mapped:
+    """An anonymous private mapping made with libc mmap, so the test controls its address: the
+    stand-in for a big malloc() (glibc serves those by mmap and frees them by munmap)."""
+    libc = ctypes.CDLL(None, use_errno=True)
+    libc.mmap.restype = ctypes.c_void_p
+    libc.mmap.argtypes = [ctypes.c_void_p, ctypes.c_size_t, ctypes.c_int, ctypes.c_int, ctypes.c_int, ctypes.c_long]
+    libc.munmap.argtypes = [ctypes.c_void_p, ctypes.c_size_t]
+    PROT_RW, MAP_PRIVATE, MAP_ANON, MAP_FIXED = 3, 0x02, 0x20, 0x10
+
+    def __init__(self, n, at=None):
+        flags = self.MAP_PRIVATE | self.MAP_ANON | (self.MAP_FIXED if at else 0)
+        self.n = n
+        self.ptr = self.libc.mmap(at, n, self.PROT_RW, flags, -1, 0)
+        assert self.ptr and self.ptr != ctypes.c_void_p(-1).value
+        assert at is None or self.ptr == at
+        self.a = np.ctypeslib.as_array((ctypes.c_ubyte * n).from_address(self.ptr))
+
+    def unmap(self):
+        self.a = None
+        assert self.libc.munmap(self.ptr, self.n) == 0
+
+
+def test_repeated_pageable_buffers_get_pinned_and_stay_correct(pkg, orc):
+    """The reference harness reuses two malloc'ed buffers for ten calls (aes-modes/test.c:287-350): the
+    second call on the same (pointer, length) pins the range, later calls DMA it directly.  Output is
+    checked against the oracle every time, with the input changing between calls."""
+    L = pkg.lib()
+    n = 96 * MIB + 16 * 7
+    key = bytes(range(16))
+    rk, nr = G.sched(pkg, key, ENC)
+    nc = bytes.fromhex("00112233445566778899aabbccddeeff")
+    src, dst = Mapped(n), Mapped(n)
+    rng = np.random.default_rng(31)
+    on, before = _reg_stats(pkg)
+    for call in range(4):
+        src.a[:] = np.resize(rng.integers(0, 256, 1 << 22, dtype=np.uint8), n)
+        dst.a[:] = 0
+        pkg.check(L.bc_aes_ctr_host(rk.ctypes.data, nr, nc, 128, call, src.ptr, dst.ptr, n, None))
+        shifted = (int.from_bytes(nc, "big") + call).to_bytes(16, "big")
+        for lo in (0, n // 2 // 16 * 16, n - MIB):                       # windows incl. the ragged tail
+            nc_w = (int.from_bytes(shifted, "big") + lo // 16).to_bytes(16, "big")
+            assert np.array_equal(dst.a[lo:lo + MIB], orc.aes_ctr(key, nc_w, src.a[lo:lo + MIB])[0]), (call, lo)
+    on, after = _reg_stats(pkg)
+    if on:                                                             # frame numbers readable: the cache must have engaged
+        assert after[0] - before[0] == 2 and after[1] - before[1] >= 4, (before, after)   # src + dst pinned once, hit on calls 3 and 4
+    src.unmap()
+    dst.unmap()
+
+
+def test_freed_and_reused_addresses_are_noticed(pkg, orc):
+    """free() + malloc() can hand the same addresses back with different physical pages behind them.
+    A registration kept across that would DMA the old pages; the library compares the frame number of
+    every page before each use and must drop the stale entry.  Here: pin a range (two calls), unmap it,
+    map NEW memory at the very same address with other contents, call again — the output must belong to
+    the new contents, and the stale drop must be counted."""
+    L = pkg.lib()
+    n = 80 * MIB
+    key = bytes(range(1, 33))
+    rk, nr = G.sched(pkg, key, ENC)
+    iv = bytes(range(16))
+    rng = np.random.default_rng(32)
+    dst = Mapped(n)
+    a = Mapped(n)
+    addr = a.ptr
+    a.a[:] = np.resize(rng.integers(0, 256, 1 << 22, dtype=np.uint8), n)
+    for _ in range(2):                                                  # second call pins it
+        pkg.check(L.bc_aes_ecb_host(rk.ctypes.data, nr, ENC, a.ptr, dst.ptr, n))
+    on, mid = _reg_stats(pkg)
+    a.unmap()
+    b = Mapped(n, at=addr)                                              # same addresses, fresh pages
+    fresh = np.resize(rng.integers(0, 256, 1 << 22, dtype=np.uint8), n)
+    b.a[:] = fresh
+    dst.a[:] = 0
+    pkg.check(L.bc_aes_ecb_host(rk.ctypes.data, nr, ENC, b.ptr, dst.ptr, n))
+    for lo in (0, n // 2, n - MIB):
+        assert np.array_equal(dst.a[lo:lo + MIB], orc.aes_ecb(key, ENC, fresh[lo:lo + MIB])), lo
+    on, end = _reg_stats(pkg)
+    if on:
+        assert end[2] - mid[2] >= 1, (mid, end)                         # the stale registration was dropped
+    # and the new mapping earns its own registration on the next sighting
+    pkg.check(L.bc_aes_ecb_host(rk.ctypes.data, nr, ENC, b.ptr, dst.ptr, n))
+    assert np.array_equal(dst.a[:MIB], orc.aes_ecb(key, ENC, fresh[:MIB]))
+    pkg.check(L.bc_shutdown())                                          # releases every registration before the unmap
+    b.unmap()
+    dst.unmap()
