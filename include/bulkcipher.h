@@ -198,6 +198,23 @@ int bc_arc4_batch_host(size_t n_streams, const void *keys, unsigned keylen, size
                        const void *in, void *out, const void *ctx_in, void *ctx_out);
 int bc_xor_host(const void *a, const void *b, void *out, size_t nbytes);
 
+/* Registration cache for pageable host buffers (off by default).  The reference's harnesses
+ * malloc() a buffer once and pass it to the API ten times (aes-modes/test.c:287-350); pageable
+ * memory has to be staged through pinned buffers by host memcpy, pinned memory is DMA'd directly.
+ * With the cache on, a range of at least 64 MiB that a bc_*_host call (or a drop-in built on one)
+ * sees for the second time is pinned in place (cudaHostRegister) and later calls take the pinned
+ * path.  Every use re-checks, from /proc/self/pagemap, that each page of the range is still the
+ * physical page that was pinned, so freed-and-reused addresses are noticed and fall back to
+ * staging; that needs CAP_SYS_ADMIN (frame numbers are hidden otherwise) and the call returns 0
+ * where it cannot be had.  It stays opt-in because of what the library cannot see: between the
+ * caller's free() and the library's next look at those addresses CUDA still holds them as
+ * registered, and an unrelated cudaHostAlloc / cudaHostRegister that lands there fails with
+ * cudaErrorAlreadyMapped.  Call bc_register_pageable(0) — it releases every idle registration —
+ * before freeing big buffers in a process that also pins memory elsewhere.  Returns 1 if the cache
+ * is on after the call, else 0.  BULKCIPHER_REGISTER_PAGEABLE=1 in the environment switches it on
+ * for unmodified callers (e.g. the relinked reference harness). */
+int bc_register_pageable(int enable);
+
 /* ---- multi-GPU (one host thread per GPU, no collective) ------------------ */
 /* The reference's slice drivers with a device per slice instead of a core per slice
  * (aes-modes/test.c:28-44 ECB, :194-206 AES-NI ECB, :273-285 CTR; test.c:44-58 RC4 XOR):

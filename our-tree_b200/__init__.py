@@ -53,6 +53,7 @@ BC_SYMBOLS = [
     "bc_aes_ecb_host_multi", "bc_aes_cbc_decrypt_host_multi", "bc_aes_cfb128_decrypt_host_multi",
     "bc_aes_cbc_encrypt_batch_host_multi", "bc_aes_cfb128_encrypt_batch_host_multi", "bc_arc4_batch_host_multi",
     "bc_device_numa_node", "bc_bind_host_thread_to_device", "bc_fill_splitmix64_dev", "bc_void_status",
+    "bc_register_pageable",
 ]
 
 
@@ -133,6 +134,7 @@ def lib() -> C.CDLL:
     L.bc_aes_invert_key.restype = None
     L.bc_set_device.argtypes = [i32]
     L.bc_internal_reg_stats.argtypes = [vp]
+    L.bc_register_pageable.argtypes = [i32]
     L.aes_setkey_enc.argtypes = [vp, vp, u32]
     L.aes_setkey_dec.argtypes = [vp, vp, u32]
     L.aes_crypt_ecb.argtypes = [vp, i32, vp, vp]

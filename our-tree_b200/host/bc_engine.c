@@ -462,15 +462,25 @@ static int classify(const void *p)
  * So a large range that is seen a SECOND time is pinned in place (cudaHostRegister) and kept in a
  * small LRU table; later calls on it take the pinned path.
  *
- * The danger of keeping a registration is a caller that frees the buffer and gets the same
- * addresses back from a later malloc: the stale registration would still point at the OLD physical
- * pages.  Nothing is assumed about that: the physical frame number of every page of the range is
- * recorded at registration (from /proc/self/pagemap) and compared again before each use — pinned
- * pages cannot move, so any difference means the range was unmapped or remapped; the entry is then
- * dropped and the call is staged.  The kernel shows frame numbers only to privileged processes
- * (CAP_SYS_ADMIN); where it does not, the cache stays off and pageable callers are staged as before.
- * BULKCIPHER_REGISTER_PAGEABLE=0 turns it off, BULKCIPHER_REGISTER_MIN_MIB (default 64) sets the
- * smallest range worth pinning, BULKCIPHER_REGISTER_MAX_GIB (default 16) caps the pinned total. */
+ * Keeping a registration has two hazards, both from a caller that frees a buffer the cache still
+ * holds (the library is not told about free()):
+ *  1. a later malloc can hand the same addresses back with different physical pages, and the stale
+ *     registration would still point at the OLD pages.  Nothing is assumed about that: the physical
+ *     frame number of every page of the range is recorded at registration (/proc/self/pagemap) and
+ *     compared again for every use — pinned pages cannot move, so any difference means the range was
+ *     unmapped or remapped; the entry is dropped and the call is staged.  The check runs while the
+ *     transfer is already in flight (the copies are enqueued, then the host would only wait): if it
+ *     fails, what the copy engines read from or wrote to the orphaned old pages is discarded and the
+ *     call is redone through staging.  The kernel shows frame numbers only to privileged processes
+ *     (CAP_SYS_ADMIN); where it does not, the cache cannot be switched on.
+ *  2. until the library next sees those addresses, CUDA still considers them registered, so another
+ *     cudaHostAlloc / cudaHostRegister in the process that happens to land there fails with
+ *     cudaErrorAlreadyMapped.  This the library cannot detect.
+ * Because of 2 the cache is OPT-IN: BULKCIPHER_REGISTER_PAGEABLE=1 in the environment, or
+ * bc_register_pageable(1); a host that frees big buffers and also pins memory elsewhere should call
+ * bc_register_pageable(0) (drops every idle registration) before it frees them.
+ * BULKCIPHER_REGISTER_MIN_MIB (default 64) sets the smallest range worth pinning,
+ * BULKCIPHER_REGISTER_MAX_GIB (default 16) caps the pinned total. */
 #include <fcntl.h>
 
 #define BC_REG_SLOTS 40
@@ -511,12 +521,12 @@ static int read_pfns(uintptr_t lo, size_t npages, uint64_t *out)
     return 0;
 }
 
-static void reg_init(void)
+static int g_reg_capable = -1;     /* frame numbers readable? (probed once) */
+
+static void reg_probe(void)
 {
-    g_reg_mode = 0;
-    const char *e = getenv("BULKCIPHER_REGISTER_PAGEABLE");
-    if (e && *e == '0') return;
-    e = getenv("BULKCIPHER_REGISTER_MIN_MIB");
+    g_reg_capable = 0;
+    const char *e = getenv("BULKCIPHER_REGISTER_MIN_MIB");
     if (e && atol(e) >= 1) g_reg_min = (size_t)atol(e) << 20;
     e = getenv("BULKCIPHER_REGISTER_MAX_GIB");
     if (e && atol(e) >= 1) g_reg_cap = (size_t)atol(e) << 30;
@@ -528,7 +538,14 @@ static void reg_init(void)
     uint64_t v;
     if (read_pfns((uintptr_t)&probe, 1, &v) != 0) { close(g_reg_fd); g_reg_fd = -1; return; }
     (void)probe;
-    g_reg_mode = 1;
+    g_reg_capable = 1;
+}
+
+static void reg_init(void)
+{
+    if (g_reg_capable < 0) reg_probe();
+    const char *e = getenv("BULKCIPHER_REGISTER_PAGEABLE");
+    g_reg_mode = (e && *e == '1' && g_reg_capable) ? 1 : 0;       /* opt-in, see above */
 }
 
 /* called with g_reg_mu held; the entry must have no users */
@@ -568,20 +585,16 @@ static int reg_acquire(const void *p, size_t n, int pageable)
         if (r->users == 0 && (!lru || r->tick < lru->tick)) lru = r;
     }
     int ok = 0;
+    if (hit) {
+        hit->users++; hit->tick = ++g_reg_tick;
+        pthread_mutex_unlock(&g_reg_mu);
+        return 2;            /* ours: held; reg_validate() decides whether it still covers the same pages */
+    }
     /* memory we did not pin ourselves (the caller's own cudaHostAlloc / cudaHostRegister) or too small to be worth it */
     if (!hit && (!pageable || n < g_reg_min)) { pthread_mutex_unlock(&g_reg_mu); return 0; }
     uint64_t *now = (uint64_t *)malloc(npages * 8);
     if (!now) { pthread_mutex_unlock(&g_reg_mu); return 0; }
-    if (hit) {
-        /* still the same physical pages as when it was pinned? */
-        const size_t first = (size_t)((plo - (hit->lo & ~((uintptr_t)g_page - 1))) / (uintptr_t)g_page);
-        if (read_pfns(plo, npages, now) == 0 && memcmp(now, hit->pfn + first, npages * 8) == 0) {
-            hit->users++; hit->tick = ++g_reg_tick; g_reg_stats[1]++; ok = 1;
-        } else if (hit->users == 0) {
-            g_reg_stats[2]++;
-            reg_drop(hit);                               /* freed and reused addresses: forget it, stage this call */
-        }
-    } else if (same && same->state == 1) {
+    if (same && same->state == 1) {
         /* second sighting: pin it.  Ranges that overlap it without containing it must go first. */
         int blocked = 0;
         for (int i = 0; i < BC_REG_SLOTS; i++) {
@@ -618,6 +631,47 @@ static int reg_acquire(const void *p, size_t n, int pageable)
     return ok;
 }
 
+/* Is the held range [p, p+n) still backed by the pages that were pinned?  (Reads the page tables:
+ * about 1 ms per GiB — callers overlap it with the transfer.) */
+static int reg_validate(const void *p, size_t n)
+{
+    const uintptr_t lo = (uintptr_t)p, hi = lo + n;
+    const uintptr_t plo = lo & ~((uintptr_t)g_page - 1);
+    const size_t npages = (size_t)((hi - 1 - plo) / (uintptr_t)g_page) + 1;
+    uint64_t *now = (uint64_t *)malloc(npages * 8);
+    if (!now) return 0;
+    int ok = read_pfns(plo, npages, now) == 0;
+    pthread_mutex_lock(&g_reg_mu);
+    const bc_reg *hit = NULL;
+    for (int i = 0; i < BC_REG_SLOTS; i++)
+        if (g_reg[i].state == 2 && g_reg[i].lo <= lo && hi <= g_reg[i].hi) hit = &g_reg[i];
+    if (ok && hit) {
+        const size_t first = (size_t)((plo - (hit->lo & ~((uintptr_t)g_page - 1))) / (uintptr_t)g_page);
+        ok = memcmp(now, hit->pfn + first, npages * 8) == 0;
+    } else {
+        ok = 0;
+    }
+    g_reg_stats[ok ? 1 : 2]++;
+    pthread_mutex_unlock(&g_reg_mu);
+    free(now);
+    return ok;
+}
+
+/* Give up the hold on a range found stale and retire the registration (once nobody else holds it). */
+static void reg_release_stale(const void *p, size_t n)
+{
+    const uintptr_t lo = (uintptr_t)p, hi = lo + n;
+    pthread_mutex_lock(&g_reg_mu);
+    for (int i = 0; i < BC_REG_SLOTS; i++) {
+        bc_reg *r = &g_reg[i];
+        if (r->state == 2 && r->users > 0 && r->lo <= lo && hi <= r->hi) {
+            if (--r->users == 0) reg_drop(r);
+            break;
+        }
+    }
+    pthread_mutex_unlock(&g_reg_mu);
+}
+
 static void reg_release(const void *p, size_t n)
 {
     const uintptr_t lo = (uintptr_t)p, hi = lo + n;
@@ -636,7 +690,19 @@ static void reg_shutdown(void)
     pthread_mutex_unlock(&g_reg_mu);
 }
 
-/* test hook: registrations, hits, stale drops, evictions so far; returns 1 if the cache is active */
+int bc_register_pageable(int enable)
+{
+    pthread_mutex_lock(&g_reg_mu);
+    if (g_reg_capable < 0) reg_probe();
+    g_reg_mode = (enable && g_reg_capable) ? 1 : 0;
+    if (!g_reg_mode)
+        for (int i = 0; i < BC_REG_SLOTS; i++) if (g_reg[i].state && g_reg[i].users == 0) reg_drop(&g_reg[i]);
+    const int on = g_reg_mode;
+    pthread_mutex_unlock(&g_reg_mu);
+    return on;
+}
+
+/* test hook: registrations, validated uses, stale drops, evictions so far; returns 1 if the cache is active */
 int bc_internal_reg_stats(uint64_t out[4])
 {
     pthread_mutex_lock(&g_reg_mu);
@@ -663,9 +729,33 @@ static void hold_add(reg_hold *h, const void *p, size_t n)
     if (c != 2) h->held[i] = reg_acquire(p, n, c == 0);
 }
 
+static __thread reg_hold *tls_hold;      /* the operands of the host call this thread is inside */
+
+/* Check the held ranges that still await it; returns the number found stale.  Stale ones are
+ * released and retired, so that classify() sees plain pageable memory afterwards. */
+static int hold_validate(reg_hold *h)
+{
+    int stale = 0;
+    for (int i = 0; h && i < h->count; i++) {
+        if (h->held[i] != 2) continue;
+        if (reg_validate(h->p[i], h->n[i])) { h->held[i] = 1; continue; }
+        reg_release_stale(h->p[i], h->n[i]);
+        h->held[i] = 0;
+        stale++;
+    }
+    return stale;
+}
+
+static int hold_pending(const reg_hold *h)
+{
+    for (int i = 0; h && i < h->count; i++) if (h->held[i] == 2) return 1;
+    return 0;
+}
+
 static void hold_begin(reg_hold *h, const void *a, size_t na, const void *b, size_t nb, const void *c, size_t nc)
 {
     h->count = 0;
+    tls_hold = h;
     hold_add(h, a, na);
     hold_add(h, b, nb);
     hold_add(h, c, nc);
@@ -674,6 +764,7 @@ static void hold_begin(reg_hold *h, const void *a, size_t na, const void *b, siz
 static void hold_end(reg_hold *h)
 {
     for (int i = 0; i < h->count; i++) if (h->held[i]) reg_release(h->p[i], h->n[i]);
+    tls_hold = NULL;
 }
 
 /* wait for a slot's previous chunk and finish its staged copy-out */
@@ -697,7 +788,7 @@ typedef int (*chunk_fn)(void *arg, size_t chunk_idx, size_t off, size_t n, void 
  * one, kernels on the second, D2H copies on the third — with events handing each slot from
  * stage to stage and back.  Both copy engines then run without waiting for the host. */
 static int run_pipeline_enqueued(bc_dev *d, const unsigned char *in, unsigned char *out, size_t nbytes,
-                                 size_t chunk, chunk_fn fn, void *arg)
+                                 size_t chunk, chunk_fn fn, void *arg, int *stale)
 {
     int rc = BC_OK;
     size_t idx = 0;
@@ -719,6 +810,9 @@ static int run_pipeline_enqueued(bc_dev *d, const unsigned char *in, unsigned ch
         BC_CUDA(cudaMemcpyAsync(out + off, s->d_buf, n, cudaMemcpyDeviceToHost, d->s_d2h), "cudaMemcpyAsync D2H");
         BC_CUDA(cudaEventRecord(d->e_d2h[sl], d->s_d2h), "cudaEventRecord");
     }
+    /* everything is enqueued and the host would only wait now: the time to check that ranges the
+     * registration cache vouched for still cover the pages that were pinned */
+    if (stale) *stale = hold_validate(tls_hold);
     cudaError_t e1 = cudaStreamSynchronize(d->s_d2h), e2 = cudaStreamSynchronize(d->s_k), e3 = cudaStreamSynchronize(d->s_h2d);
     if (rc == BC_OK && e1 != cudaSuccess) rc = bc_cuda_fail((int)e1, "cudaStreamSynchronize(D2H)");
     if (rc == BC_OK && e2 != cudaSuccess) rc = bc_cuda_fail((int)e2, "cudaStreamSynchronize(kernels)");
@@ -729,9 +823,20 @@ static int run_pipeline_enqueued(bc_dev *d, const unsigned char *in, unsigned ch
 static int run_pipeline(bc_dev *d, const unsigned char *in, unsigned char *out, size_t nbytes,
                         size_t chunk, chunk_fn fn, void *arg)
 {
-    const int in_pinned = in && classify(in) == 1, out_pinned = classify(out) == 1;
-    if ((in_pinned || !in) && out_pinned && !getenv("BULKCIPHER_HOST_IN_LOOP"))
-        return run_pipeline_enqueued(d, in, out, nbytes, chunk, fn, arg);
+    int in_pinned = in && classify(in) == 1, out_pinned = classify(out) == 1;
+    if ((in_pinned || !in) && out_pinned && !getenv("BULKCIPHER_HOST_IN_LOOP")) {
+        int stale = 0;
+        int rc0 = run_pipeline_enqueued(d, in, out, nbytes, chunk, fn, arg, &stale);
+        if (!stale) return rc0;
+        /* a registration turned out to be stale (freed and re-mapped addresses): the copy engines
+         * worked on orphaned pages, nothing of the caller's was read or written.  The entries are
+         * retired; do the whole transfer again through staging (same chunking: batched calls cut
+         * their chunks on item boundaries). */
+    } else if (hold_pending(tls_hold)) {
+        hold_validate(tls_hold);                      /* host-in-the-loop path: check before anything moves */
+    }
+    in_pinned = in && classify(in) == 1;
+    out_pinned = classify(out) == 1;
     int rc = BC_OK;
     size_t idx = 0;
     for (size_t off = 0; off < nbytes && rc == BC_OK; off += chunk, idx++) {

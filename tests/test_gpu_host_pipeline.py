@@ -179,6 +179,7 @@ def test_repeated_pageable_buffers_get_pinned_and_stay_correct(pkg, orc):
     nc = bytes.fromhex("00112233445566778899aabbccddeeff")
     src, dst = Mapped(n), Mapped(n)
     rng = np.random.default_rng(31)
+    L.bc_register_pageable(1)                                          # opt-in; 0 back if frame numbers are hidden
     on, before = _reg_stats(pkg)
     for call in range(4):
         src.a[:] = np.resize(rng.integers(0, 256, 1 << 22, dtype=np.uint8), n)
@@ -191,6 +192,7 @@ def test_repeated_pageable_buffers_get_pinned_and_stay_correct(pkg, orc):
     on, after = _reg_stats(pkg)
     if on:                                                             # frame numbers readable: the cache must have engaged
         assert after[0] - before[0] == 2 and after[1] - before[1] >= 4, (before, after)   # src + dst pinned once, hit on calls 3 and 4
+    assert L.bc_register_pageable(0) == 0                              # releases the registrations BEFORE the memory goes away
     src.unmap()
     dst.unmap()
 
@@ -210,6 +212,7 @@ def test_freed_and_reused_addresses_are_noticed(pkg, orc):
     dst = Mapped(n)
     a = Mapped(n)
     addr = a.ptr
+    L.bc_register_pageable(1)
     a.a[:] = np.resize(rng.integers(0, 256, 1 << 22, dtype=np.uint8), n)
     for _ in range(2):                                                  # second call pins it
         pkg.check(L.bc_aes_ecb_host(rk.ctypes.data, nr, ENC, a.ptr, dst.ptr, n))
@@ -228,6 +231,6 @@ def test_freed_and_reused_addresses_are_noticed(pkg, orc):
     # and the new mapping earns its own registration on the next sighting
     pkg.check(L.bc_aes_ecb_host(rk.ctypes.data, nr, ENC, b.ptr, dst.ptr, n))
     assert np.array_equal(dst.a[:MIB], orc.aes_ecb(key, ENC, fresh[:MIB]))
-    pkg.check(L.bc_shutdown())                                          # releases every registration before the unmap
+    L.bc_register_pageable(0)                                           # releases every registration before the unmap
     b.unmap()
     dst.unmap()
