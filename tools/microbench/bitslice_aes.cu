@@ -347,9 +347,10 @@ int main(int argc, char **argv)
         if (ms < best) { best = ms; CK(cudaMemcpy(&cyc, d_cyc, 8, cudaMemcpyDeviceToHost)); }
     }
     const double blocks = (double)nt * 32 * iters;
-    const double blk_per_clk_sm = (double)occ * BS_THREADS * 32 * iters / (double)cyc;     // per SM, from clock64 of CTA 0
-    printf("time %.3f ms, %lld clk in CTA 0 (%.0f MHz effective), %.4f blocks/clk/SM = %.3f B/clk/SM\n",
-           best, cyc, cyc / (best * 1e3), blk_per_clk_sm, 16 * blk_per_clk_sm);
+    const double clk_per_s = khz * 1e3;                                      // nominal SM clock (1.965 GHz on B200)
+    const double blk_per_clk_sm = blocks / (best * 1e-3) / clk_per_s / sms;
+    printf("time %.3f ms -> %.4f blocks/clk/SM = %.3f B/clk/SM at the nominal %.0f MHz (CTA 0 counted %lld clock64 ticks)\n",
+           best, blk_per_clk_sm, 16 * blk_per_clk_sm, khz / 1e3, cyc);
     printf("core-only throughput %.1f GB/s (16 B x %.3g blocks / %.3f ms); table kernel: 3.5 B/clk/SM, 1024 GB/s end to end\n",
            blocks * 16 / (best * 1e6), blocks, best);
     return 0;
