@@ -112,8 +112,10 @@ def test_reference_aes_gpu_mains_built_against_the_facade(orc):
     import numpy as np
     dec, enc = _need("ref_aes_gpu_ecb_d", "ref_aes_gpu_ecb_e")
     pt = "00112233445566778899AABBCCDDEEFF"
+    # (FIPS-197 C.2's 24-byte key is left out: the reference's own key parser, main_ecb_d.cu:43-51, sscanf's
+    # "%02X" — an unsigned int — into a byte array and so writes 3 bytes past a malloc(24), which glibc
+    # detects; malloc(16) and malloc(32) happen to have the slack.  AES-192 is covered by the facade test above.)
     for key, ct in (("000102030405060708090A0B0C0D0E0F", "69C4E0D86A7B0430D8CDB78070B4C55A"),
-                    ("000102030405060708090A0B0C0D0E0F1011121314151617", "DDA97CA4864CDFE06EAF70A0EC0D7191"),
                     ("000102030405060708090A0B0C0D0E0F101112131415161718191A1B1C1D1E1F", "8EA2B7CA516745BFEAFC49904B496089")):
         assert run([dec, key, ct]).strip() == pt
     rng = np.random.default_rng(3)
