@@ -644,6 +644,17 @@ def run_ours(args):
     hout = np.ctypeslib.as_array((ctypes.c_ubyte * (1 << 20)).from_address(h_out))
     if not np.array_equal(hout, d_chk_out.cpu().numpy()):
         raise SystemExit("e2e output differs from the device-resident path")
+    # ... and 1 MiB windows across the pipeline's chunk seams (the ramp starts with 4 / 8 / 16 / 32 MiB chunks) and the end
+    hall = np.ctypeslib.as_array((ctypes.c_ubyte * window).from_address(h_out))
+    for woff in (3 << 20, 11 << 20, 27 << 20, 59 << 20, window // 2, window - (1 << 20)):
+        if woff + (1 << 20) > window:
+            continue
+        d_chk.copy_(torch.from_numpy(hin[woff:woff + (1 << 20)].copy()))
+        pkg.check(L.bc_aes_ctr_dev(rk.ctypes.data, nr, COUNTER, 128, fb_last + woff // 16, d_chk.data_ptr(), d_chk_out.data_ptr(),
+                                   1 << 20, None, st))
+        torch.cuda.synchronize()
+        if not np.array_equal(hall[woff:woff + (1 << 20)], d_chk_out.cpu().numpy()):
+            raise SystemExit(f"e2e output differs from the device-resident path at host offset {woff}")
     chk, _ = checker()
     nc = ((int.from_bytes(COUNTER, "big") + fb_last) % (1 << 128)).to_bytes(16, "big")
     if not np.array_equal(hout[:65536], chk.aes_ctr(KEY, nc, hin[:65536])[0]):

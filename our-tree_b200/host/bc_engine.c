@@ -729,6 +729,7 @@ static void hold_add(reg_hold *h, const void *p, size_t n)
     if (c != 2) h->held[i] = reg_acquire(p, n, c == 0);
 }
 
+static __thread int tls_ramp;            /* this thread's current host call accepts chunks of any size (CTR, ECB, XOR) */
 static __thread reg_hold *tls_hold;      /* the operands of the host call this thread is inside */
 
 /* Check the held ranges that still await it; returns the number found stale.  Stale ones are
@@ -792,8 +793,28 @@ static int run_pipeline_enqueued(bc_dev *d, const unsigned char *in, unsigned ch
 {
     int rc = BC_OK;
     size_t idx = 0;
-    for (size_t off = 0; off < nbytes && rc == BC_OK; off += chunk, idx++) {
-        const size_t n = nbytes - off < chunk ? nbytes - off : chunk;
+    /* Ramp (position-independent chunks only, tls_ramp): while the first chunk travels in, nothing
+     * travels out, and the other way round at the end — one link direction idles for a whole chunk at
+     * each end.  Starting and finishing with chunks of 1/16, 1/8, 1/4, 1/2 of the granule shrinks
+     * those two single-direction phases 16-fold. */
+    const int ramp = tls_ramp && nbytes >= 8 * chunk && (chunk >> 4) >= ((size_t)1 << 20) && !getenv("BULKCIPHER_NO_RAMP");
+    size_t n = 0;
+    for (size_t off = 0; off < nbytes && rc == BC_OK; off += n, idx++) {
+        n = chunk;
+        if (ramp) {
+            const size_t left = nbytes - off, q = chunk >> 4, tail_total = chunk - q;   /* 1/2 + 1/4 + 1/8 + 1/16 */
+            if (idx < 4) {
+                n = chunk >> (4 - idx);                                  /* head: 1/16, 1/8, 1/4, 1/2 */
+            } else if (left > tail_total && ((left - tail_total) & ~(size_t)4095) > 0) {
+                n = (left - tail_total) & ~(size_t)4095;                 /* middle: full granules, then what is left of it */
+                if (n > chunk) n = chunk;
+            } else {
+                n = chunk >> 1;                                          /* tail: 1/2, 1/4, 1/8, 1/16 (+ the odd bytes) */
+                while (n > q && left < 2 * n - q) n >>= 1;
+                if (n == q) n = left;
+            }
+        }
+        if (n > nbytes - off) n = nbytes - off;
         const int sl = (int)(idx % BC_SLOTS);
         bc_slot *s = &d->slot[sl];
         if (in) {
@@ -947,7 +968,9 @@ int bc_aes_ctr_host(const uint32_t *rk, int nr, const unsigned char counter[16],
     pthread_mutex_lock(&d->lock);
     if ((rc = dev_ensure_slots(d)) == BC_OK && (rc = dev_ensure_aux(d, 16)) == BC_OK) {
         ctr_op o = { rk, nr, counter, counter_bits, first_block, nbytes, last_keystream ? d->d_aux : NULL };
+        tls_ramp = 1;
         rc = run_pipeline(d, (const unsigned char *)in, (unsigned char *)out, nbytes, pick_chunk(nbytes, in, out), ctr_chunk, &o);
+        tls_ramp = 0;
         if (rc == BC_OK && last_keystream) rc = bc_memcpy_d2h(last_keystream, d->d_aux, 16);
     }
     pthread_mutex_unlock(&d->lock);
@@ -983,7 +1006,9 @@ static int ecb_host(int be32, const uint32_t *rk, int nr, int mode, const void *
     pthread_mutex_lock(&d->lock);
     if ((rc = dev_ensure_slots(d)) == BC_OK) {
         ecb_op o = { rk, nr, mode, be32 };
+        tls_ramp = 1;
         rc = run_pipeline(d, (const unsigned char *)in, (unsigned char *)out, nbytes, pick_chunk(nbytes, in, out), ecb_chunk, &o);
+        tls_ramp = 0;
     }
     pthread_mutex_unlock(&d->lock);
     hold_end(&h);

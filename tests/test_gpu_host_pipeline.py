@@ -234,3 +234,43 @@ def test_freed_and_reused_addresses_are_noticed(pkg, orc):
     L.bc_register_pageable(0)                                           # releases every registration before the unmap
     b.unmap()
     dst.unmap()
+
+
+def test_ramped_chunk_schedule_subprocess():
+    """Pinned CTR / ECB transfers of >= 8 granules start and end with chunks of 1/16 .. 1/2 granule
+    (host/bc_engine.c, run_pipeline_enqueued).  With the default 64 MiB granule that needs 512 MiB;
+    a child process with a 16 MiB granule exercises the same schedule on 150 MiB (+ a ragged CTR
+    tail) and compares every byte with the device-resident path."""
+    import os
+    import subprocess
+    import sys
+    root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+    code = r'''
+import ctypes, sys, numpy as np, torch
+sys.path.insert(0, %r)
+import __graft_entry__ as g
+pkg = g.load_package(); L = pkg.lib()
+n = 150 * (1 << 20) + 4096 * 3 + 21
+rc, ctx = pkg.aes_setkey_enc(bytes(range(16))); rk = pkg.schedule_words(ctx)
+nc = bytes.fromhex("000102030405060708090a0bfffffff0")
+h_in, h_out = L.bc_host_alloc(n), L.bc_host_alloc(n)
+a = np.ctypeslib.as_array((ctypes.c_ubyte * n).from_address(h_in)); b = np.ctypeslib.as_array((ctypes.c_ubyte * n).from_address(h_out))
+a[:] = np.resize(np.random.default_rng(1).integers(0, 256, 1 << 22, dtype=np.uint8), n)
+d_in = torch.from_numpy(a.copy()).cuda(); d_out = torch.empty_like(d_in); st = torch.cuda.current_stream().cuda_stream
+for ramp in ("", "1"):
+    # BULKCIPHER_NO_RAMP is read per call: the same bytes must come out with and without the ramp
+    import os
+    if ramp: os.environ["BULKCIPHER_NO_RAMP"] = "1"
+    pkg.check(L.bc_aes_ctr_host(rk.ctypes.data, 10, nc, 128, 5, h_in, h_out, n, None))
+    pkg.check(L.bc_aes_ctr_dev(rk.ctypes.data, 10, nc, 128, 5, d_in.data_ptr(), d_out.data_ptr(), n, None, st)); torch.cuda.synchronize()
+    assert np.array_equal(b, d_out.cpu().numpy()), "CTR"
+    m = n // 16 * 16
+    pkg.check(L.bc_aes_ecb_host(rk.ctypes.data, 10, 1, h_in, h_out, m))
+    pkg.check(L.bc_aes_ecb_dev(rk.ctypes.data, 10, 1, d_in.data_ptr(), d_out.data_ptr(), m, st)); torch.cuda.synchronize()
+    assert np.array_equal(b[:m], d_out.cpu().numpy()[:m]), "ECB"
+print("RAMP_OK")
+''' % root
+    env = dict(os.environ, BULKCIPHER_CHUNK_MIB="16")
+    env.pop("BULKCIPHER_NO_RAMP", None)
+    p = subprocess.run([sys.executable, "-c", code], capture_output=True, text=True, env=env, timeout=600)
+    assert p.returncode == 0 and "RAMP_OK" in p.stdout, p.stdout[-2000:] + p.stderr[-3000:]
