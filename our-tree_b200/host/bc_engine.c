@@ -566,7 +566,7 @@ static int reg_acquire(const void *p, size_t n, int pageable)
     if (!p || n == 0) return 0;
     pthread_mutex_lock(&g_reg_mu);
     if (g_reg_mode < 0) reg_init();
-    if (g_reg_mode == 0) { pthread_mutex_unlock(&g_reg_mu); return 0; }
+    if (g_reg_total == 0 && g_reg_mode == 0) { pthread_mutex_unlock(&g_reg_mu); return 0; }   /* off and nothing of ours alive */
     const uintptr_t lo = (uintptr_t)p, hi = lo + n;
     /* A range that straddles one of our registrations (overlaps without lying inside it) would look
      * pinned at one end and pageable at the other: retire that registration first. */
@@ -590,10 +590,11 @@ static int reg_acquire(const void *p, size_t n, int pageable)
         pthread_mutex_unlock(&g_reg_mu);
         return 2;            /* ours: held; reg_validate() decides whether it still covers the same pages */
     }
-    /* memory we did not pin ourselves (the caller's own cudaHostAlloc / cudaHostRegister) or too small to be worth it */
-    if (!hit && (!pageable || n < g_reg_min)) { pthread_mutex_unlock(&g_reg_mu); return 0; }
-    uint64_t *now = (uint64_t *)malloc(npages * 8);
-    if (!now) { pthread_mutex_unlock(&g_reg_mu); return 0; }
+    /* switched off (only registrations still in use by other calls are alive), memory we did not pin
+     * ourselves (the caller's own cudaHostAlloc / cudaHostRegister), or too small to be worth it */
+    if (g_reg_mode == 0 || !pageable || n < g_reg_min) { pthread_mutex_unlock(&g_reg_mu); return 0; }
+    uint64_t *now = NULL;
+    if (same && same->state == 1 && !(now = (uint64_t *)malloc(npages * 8))) { pthread_mutex_unlock(&g_reg_mu); return 0; }
     if (same && same->state == 1) {
         /* second sighting: pin it.  Ranges that overlap it without containing it must go first. */
         int blocked = 0;
@@ -678,7 +679,10 @@ static void reg_release(const void *p, size_t n)
     pthread_mutex_lock(&g_reg_mu);
     for (int i = 0; i < BC_REG_SLOTS; i++) {
         bc_reg *r = &g_reg[i];
-        if (r->state == 2 && r->users > 0 && r->lo <= lo && hi <= r->hi) { r->users--; break; }
+        if (r->state == 2 && r->users > 0 && r->lo <= lo && hi <= r->hi) {
+            if (--r->users == 0 && g_reg_mode == 0) reg_drop(r);       /* the cache was switched off meanwhile */
+            break;
+        }
     }
     pthread_mutex_unlock(&g_reg_mu);
 }
