@@ -41,9 +41,15 @@ int aes_setkey_enc(aes_context *ctx, const unsigned char *key, unsigned int keys
 int aes_setkey_dec(aes_context *ctx, const unsigned char *key, unsigned int keysize);
 
 /* aes-modes/aes.c:650-752: one 16-byte block.  `mode` only selects the tables;
- * ctx must hold the matching schedule.  One GPU round trip per call — loop
- * callers (aes-modes/test.c:37-41) should move to AES_ECB_encrypt (aesni.h) or
- * bc_aes_ecb_host. */
+ * ctx must hold the matching schedule.  A lone call is one GPU round trip.  A
+ * thread whose calls walk consecutive addresses (the reference's loop,
+ * aes-modes/test.c:37-41) is served from a per-thread read-ahead window: the
+ * library copies the next 4 KiB .. 4 MiB of the caller's input without ever
+ * faulting (process_vm_readv), runs the window through the GPU in one call, and
+ * answers a later call from it only when that call's 16 input bytes equal the
+ * bytes the stored output was computed from (same key schedule, same mode) —
+ * exact by construction.  Bulk callers are still better off with
+ * AES_ECB_encrypt (aesni.h) or bc_aes_ecb_host. */
 int aes_crypt_ecb(aes_context *ctx, int mode, const unsigned char input[16], unsigned char output[16]);
 
 /* aes-modes/aes.c:757-816.  length % 16 != 0 -> -0x22, nothing written.  iv is

@@ -135,6 +135,8 @@ def lib() -> C.CDLL:
     L.bc_set_device.argtypes = [i32]
     L.bc_internal_reg_stats.argtypes = [vp]
     L.bc_register_pageable.argtypes = [i32]
+    L.bc_internal_ecb_ahead_stats.argtypes = [vp]
+    L.bc_internal_ecb_ahead_stats.restype = None
     L.aes_setkey_enc.argtypes = [vp, vp, u32]
     L.aes_setkey_dec.argtypes = [vp, vp, u32]
     L.aes_crypt_ecb.argtypes = [vp, i32, vp, vp]

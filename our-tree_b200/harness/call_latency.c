@@ -12,6 +12,7 @@
 #include <string.h>
 #include <time.h>
 
+#include "aes.h"
 #include "bulkcipher.h"
 
 static uint32_t rk[60];
@@ -32,6 +33,17 @@ static double now_us(void)
     struct timespec ts;
     clock_gettime(CLOCK_MONOTONIC, &ts);
     return ts.tv_sec * 1e6 + ts.tv_nsec * 1e-3;
+}
+
+typedef struct { aes_context *ctx; const unsigned char *in; unsigned char *out; size_t n; double us; } ecb_job;
+
+static void *ecb_plain(void *p)
+{
+    ecb_job *j = (ecb_job *)p;
+    const double t0 = now_us();
+    for (size_t off = 0; off < j->n; off += 16) aes_crypt_ecb(j->ctx, AES_ENCRYPT, j->in + off, j->out + off);
+    j->us = now_us() - t0;
+    return NULL;
 }
 
 static int cmp(const void *a, const void *b) { double x = *(const double *)a, y = *(const double *)b; return x < y ? -1 : x > y; }
@@ -74,6 +86,31 @@ int main(void)
         if (memcmp(b, pb, n)) { fprintf(stderr, "pageable and pinned outputs differ\n"); return 1; }
         printf("| %zu | %.0f | %.0f | %.0f | %.0f |\n", n, m1, m2, m3, m4);
         free(a); free(b); bc_host_free(pa); bc_host_free(pb);
+    }
+
+    /* the reference's "Plain ECB" loop, one aes_crypt_ecb call per 16 bytes (aes-modes/test.c:37-41) */
+    {
+        const size_t n = 16 << 20;
+        unsigned char *a = malloc(n), *b = malloc(n), *c = malloc(n);
+        aes_context ctx;
+        for (size_t i = 0; i < n; i++) a[i] = (unsigned char)(i * 131 + (i >> 11));
+        aes_setkey_enc(&ctx, key, 128);
+        const double t0 = now_us();
+        for (size_t off = 0; off < n; off += 16)
+            if (aes_crypt_ecb(&ctx, AES_ENCRYPT, a + off, b + off)) { fprintf(stderr, "aes_crypt_ecb: %s\n", bc_last_error()); return 1; }
+        const double dt = now_us() - t0;
+        if (bc_aes_ecb_host(rk, nr, BC_ENCRYPT, a, c, n) || memcmp(b, c, n)) { fprintf(stderr, "block loop differs from the bulk call\n"); return 1; }
+        printf("\naes_crypt_ecb block loop over %zu MiB (read-ahead window): %.1f ms = %.0f MB/s, equal to the bulk call\n",
+               n >> 20, dt / 1e3, n / dt);
+        /* the same loop with the window off (the switch is read when a thread makes its first call) */
+        setenv("BULKCIPHER_ECB_READAHEAD", "0", 1);
+        ecb_job ej = { &ctx, a, b, 4000 * 16, 0 };
+        pthread_t th;
+        pthread_create(&th, NULL, ecb_plain, &ej);
+        pthread_join(th, NULL);
+        printf("aes_crypt_ecb block loop, one GPU round trip per block (BULKCIPHER_ECB_READAHEAD=0): %.1f us per block = %.2f MB/s\n",
+               ej.us / 4000, 4000 * 16 / ej.us);
+        free(a); free(b); free(c);
     }
     return 0;
 }

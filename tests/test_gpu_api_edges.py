@@ -218,3 +218,71 @@ def test_resumable_calls_random_splits(pkg, orc):
         out = np.concatenate([pkg.rc4_crypt(st, p) for p in parts] + [np.zeros(0, np.uint8)])
         wout, i1, i2, perm = orc.rc4(rkey, parts)
         assert np.array_equal(out, wout) and (st.index1, st.index2, bytes(st.perm)) == (i1, i2, perm)
+
+
+# ---- aes_crypt_ecb one block per call: the per-thread read-ahead window (host/aes_dropin.c) ----
+
+def _ecb_stats(pkg):
+    import ctypes
+    out = (ctypes.c_uint64 * 2)()
+    pkg.lib().bc_internal_ecb_ahead_stats(out)
+    return out[0], out[1]
+
+
+def _walk(pkg, ctx, mode, src, dst, first, count):
+    import ctypes
+    L = pkg.lib()
+    for b in range(first, first + count):
+        assert L.aes_crypt_ecb(ctypes.byref(ctx), mode, src.ctypes.data + 16 * b, dst.ctypes.data + 16 * b) == 0
+
+
+def test_ecb_block_loop_read_ahead_is_exact(pkg, orc):
+    """The reference's loop over aes_crypt_ecb (aes-modes/test.c:37-41), 16 bytes per call: served from
+    the read-ahead window, bit-exact against the oracle — also when the caller changes the bytes ahead
+    of the walk, re-keys the context in the middle, works in place, or jumps around."""
+    rng = np.random.default_rng(77)
+    key, key2 = bytes(range(16)), bytes(range(50, 82))
+    nblk = 16384                                                        # 256 KiB
+    data = rng.integers(0, 256, 16 * nblk, dtype=np.uint8)
+    out = np.zeros_like(data)
+    rc, ctx = pkg.aes_setkey_enc(key)
+    h0, m0 = _ecb_stats(pkg)
+    _walk(pkg, ctx, ENC, data, out, 0, 6000)
+    h1, m1 = _ecb_stats(pkg)
+    assert (h1 - h0) + (m1 - m0) == 6000 and m1 - m0 < 40, (h1 - h0, m1 - m0)       # a handful of GPU trips, not 6000
+    data[16 * 6100:16 * 6200] ^= 0x5A                                   # the caller rewrites bytes the window already copied
+    _walk(pkg, ctx, ENC, data, out, 6000, 2000)
+    assert np.array_equal(out[:16 * 8000], orc.aes_ecb(key, ENC, data[:16 * 8000]))
+    import ctypes
+    assert pkg.lib().aes_setkey_enc(ctypes.byref(ctx), key2, 256) == 0  # same context object, new key, the walk goes on
+    _walk(pkg, ctx, ENC, data, out, 8000, nblk - 8000)
+    assert np.array_equal(out[16 * 8000:], orc.aes_ecb(key2, ENC, data[16 * 8000:]))
+    # decrypt in place (input == output), then random single blocks
+    rc, dctx = pkg.aes_setkey_dec(key2)
+    buf = out[16 * 8000:].copy()
+    _walk(pkg, dctx, DEC, buf, buf, 0, buf.size // 16)
+    assert np.array_equal(buf, data[16 * 8000:])
+    for b in rng.integers(0, nblk, 50):
+        _walk(pkg, ctx, ENC, data, out, int(b), 1)
+        assert np.array_equal(out[16 * b:16 * b + 16], orc.aes_ecb(key2, ENC, data[16 * b:16 * b + 16]))
+
+
+def test_ecb_read_ahead_stops_at_unmapped_memory(pkg, orc):
+    """The window is copied with process_vm_readv, one page per iovec element: a walk that ends right
+    below an unmapped page must neither fault nor return anything but the right blocks."""
+    import ctypes
+    libc = ctypes.CDLL(None, use_errno=True)
+    libc.mmap.restype = ctypes.c_void_p
+    libc.mmap.argtypes = [ctypes.c_void_p, ctypes.c_size_t, ctypes.c_int, ctypes.c_int, ctypes.c_int, ctypes.c_long]
+    libc.munmap.argtypes = [ctypes.c_void_p, ctypes.c_size_t]
+    base = libc.mmap(None, 3 * 4096, 3, 0x22, -1, 0)
+    assert base and base != ctypes.c_void_p(-1).value
+    assert libc.munmap(base + 2 * 4096, 4096) == 0                      # third page gone: reads past page 2 would fault
+    src = np.ctypeslib.as_array((ctypes.c_ubyte * 8192).from_address(base))
+    src[:] = np.random.default_rng(5).integers(0, 256, 8192, dtype=np.uint8)
+    dst = np.zeros(8192, np.uint8)
+    key = bytes(range(24))
+    rc, ctx = pkg.aes_setkey_enc(key)
+    _walk(pkg, ctx, ENC, src, dst, 0, 512)                              # every block of both pages, up to the very edge
+    assert np.array_equal(dst, orc.aes_ecb(key, ENC, src.copy()))
+    libc.munmap(base, 2 * 4096)
