@@ -607,7 +607,7 @@ def run_ours(args):
     window = e2e_bytes if (n_gpus <= 2 or roomy) else GIB
     h_in = h_out = None
     while window >= (64 << 20):
-        h_in, h_out = L.bc_host_alloc(window), L.bc_host_alloc(window)
+        h_in, h_out = (L.bc_host_alloc_wc if args.wc_input else L.bc_host_alloc)(window), L.bc_host_alloc(window)
         if h_in and h_out:
             break
         L.bc_host_free(h_in)
@@ -760,6 +760,7 @@ def main():
     ap.add_argument("--no-others", action="store_true", help="skip the configs 3/4 side measurements")
     ap.add_argument("--no-config5", action="store_true", help="skip the 256 GiB configs[4] record at N > 1")
     ap.add_argument("--no-numa-bind", action="store_true", help="A/B: leave the rank's host thread unbound")
+    ap.add_argument("--wc-input", action="store_true", help="A/B: the e2e input buffer is write-combined pinned memory")
     ap.add_argument("--shard-gib", type=float, default=4.0,
                     help="bytes per GPU in GiB (default 4 = BASELINE configs[1]; 256/N reproduces config 5)")
     args = ap.parse_args()

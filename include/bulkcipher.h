@@ -60,6 +60,7 @@ int  bc_shutdown(void);
 /* bc_memcpy_* are synchronous copies on the legacy default stream: follow them with calls on
  * stream NULL, or synchronise before using a non-blocking stream of your own. */
 void *bc_host_alloc(size_t bytes);            /* pinned host memory (cudaHostAlloc)   */
+void *bc_host_alloc_wc(size_t bytes);         /* pinned + write-combined: CPU writes, GPU reads (an H2D source); free with bc_host_free */
 void  bc_host_free(void *p);
 void *bc_dev_alloc(size_t bytes);
 void  bc_dev_free(void *p);

@@ -41,7 +41,7 @@ DROPIN_SYMBOLS = [
 ]
 BC_SYMBOLS = [
     "bc_last_error", "bc_device_count", "bc_set_device", "bc_get_device", "bc_sm_count", "bc_shutdown",
-    "bc_host_alloc", "bc_host_free", "bc_dev_alloc", "bc_dev_free", "bc_memcpy_h2d", "bc_memcpy_d2h",
+    "bc_host_alloc", "bc_host_alloc_wc", "bc_host_free", "bc_dev_alloc", "bc_dev_free", "bc_memcpy_h2d", "bc_memcpy_d2h",
     "bc_device_sync",
     "bc_aes_ctr_dev", "bc_aes_ecb_dev", "bc_aes_cbc_decrypt_dev", "bc_aes_cbc_encrypt_batch_dev",
     "bc_arc4_batch_dev", "bc_xor_dev", "bc_aes_cbc_decrypt_inplace_noalloc_dev",
@@ -93,6 +93,8 @@ def lib() -> C.CDLL:
     L.bc_host_alloc.restype = vp
     L.bc_host_alloc.argtypes = [sz]
     L.bc_host_free.argtypes = [vp]
+    L.bc_host_alloc_wc.restype = vp
+    L.bc_host_alloc_wc.argtypes = [sz]
     L.bc_dev_alloc.restype = vp
     L.bc_dev_alloc.argtypes = [sz]
     L.bc_dev_free.argtypes = [vp]

@@ -274,6 +274,17 @@ void *bc_host_alloc(size_t bytes)
     return p;
 }
 
+/* Write-combined pinned memory: for buffers the CPU only WRITES and the GPU only reads (an H2D
+ * source).  The device's reads need no cache snoop; CPU reads from it are very slow. */
+void *bc_host_alloc_wc(size_t bytes)
+{
+    void *p = NULL;
+    if (bc_set_device(tls_device)) return NULL;
+    cudaError_t e = cudaHostAlloc(&p, bytes ? bytes : 1, cudaHostAllocPortable | cudaHostAllocWriteCombined);
+    if (e != cudaSuccess) { bc_cuda_fail((int)e, "cudaHostAlloc(write-combined)"); return NULL; }
+    return p;
+}
+
 void bc_host_free(void *p) { if (p) cudaFreeHost(p); }
 
 void *bc_dev_alloc(size_t bytes)
