@@ -499,15 +499,17 @@ aes_blocks_kernel(const __grid_constant__ AesSched ks, const __grid_constant__ B
             } else if (CHAIN) {
                 /* in place: a row's loads all come before its stores, so the lane to the left can
                  * still be read from memory; only lane 0 needs the previous row's last block, which
-                 * that row's store has already overwritten — it travels in `carry` */
+                 * that row's store has already overwritten — lane 0 reads it a row early into `carry` */
                 if (live && lane != 0) prev = a.in[b - 1];
-                if (lane == 0) prev = carry;
-                carry.x = __shfl_sync(0xffffffffu, c.x, 31);
-                carry.y = __shfl_sync(0xffffffffu, c.y, 31);
-                carry.z = __shfl_sync(0xffffffffu, c.z, 31);
-                carry.w = __shfl_sync(0xffffffffu, c.w, 31);
-                /* lane L just read in[b-1], the block lane L-1 stores below: order every lane's
-                 * loads before any lane's store (a shuffle converges the warp but is no fence) */
+                if (lane == 0) {
+                    prev = carry;
+                    /* the next row's lane 0 needs this row's last ciphertext block, which lane 31 is
+                     * about to overwrite: fetch it now (one single-lane load = one wavefront, where
+                     * four warp-wide shuffles cost four on the same data pipe) */
+                    if (it + 1 < kRowsPerGroup && (full || b + 31 < a.nblocks)) carry = a.in[b + 31];
+                }
+                /* lane L just read in[b-1] (lane 0: in[b+31]), blocks other lanes store below: order every
+                 * lane's loads before any lane's store */
                 __syncwarp();
             }
             State s;
