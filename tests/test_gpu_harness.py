@@ -79,7 +79,7 @@ def test_reference_aes_harness_relinked():
     libbulkcipher.so: `AESNI CTR` CSV lines with 10 timings each (aes-modes/test.c:287-350).  Its
     buffers are malloc'ed (pageable) and its threads call AES_CTR_encrypt concurrently on slices."""
     (aes,) = _need("ref_aes_modes_test")
-    out, done = run_bounded([aes], 60, "ref_aes_modes_test.log")
+    out, done = run_bounded([aes], 35, "ref_aes_modes_test.log")
     lines = [ln for ln in out.splitlines() if ln.startswith("AESNI CTR, ")]
     if not done and lines:
         lines.pop()                                   # the harness writes unbuffered: the last line was cut by the limit
@@ -96,7 +96,7 @@ def test_reference_rc4_harness_relinked():
     """The reference's test.c the same way: every size up to 100 MB with all four thread counts within
     the limit; a FULL run also reaches the reference's closing arc4_self_test (3 x passed, GPU path)."""
     (rc4,) = _need("ref_rc4_test")
-    out, done = run_bounded([rc4], 75, "ref_rc4_test.log")
+    out, done = run_bounded([rc4], 45, "ref_rc4_test.log")
     for size in (1048576, 10485760, 104857600):
         for t in (1, 2, 4, 8):
             assert f"RC4, {size}, {t}, " in out, out[-1500:]
@@ -124,7 +124,7 @@ def test_reference_aes_gpu_mains_built_against_the_facade(orc):
     cipher = orc.aes_ecb(key, 1, plain)
     assert run([dec, key.hex().upper(), cipher.tobytes().hex().upper()]).strip() == plain.tobytes().hex().upper()
     assert "Invalid AES key size" in subprocess.run([dec, "0011", "00" * 16], capture_output=True, text=True).stdout
-    out, done = run_bounded([enc], 30, "ref_aes_gpu_ecb_e.log")
+    out, done = run_bounded([enc], 20, "ref_aes_gpu_ecb_e.log")
     assert "AES ECB test, 1048576: " in out and "AES ECB test, 10485760: " in out and out.count("Average") >= 2
     if done:
         assert out.count("Average") == 4
