@@ -92,6 +92,7 @@ typedef struct {
     unsigned char *d_buf;       /* BC_CHUNK_BYTES of HBM, processed in place */
     unsigned char *pin_in;      /* staging for pageable callers (lazy) */
     unsigned char *pin_out;
+    unsigned char *pin_b;       /* staging for a pageable second operand (bc_xor_host) */
     /* pending copy-out of a staged chunk */
     unsigned char *pend_dst;
     size_t         pend_len;
@@ -1352,7 +1353,7 @@ rc4_done:
 
 /* out = a ^ b on host buffers (arc4_crypt, arc4.c:101-112).  `a` rides the pipeline
  * buffer, `b` a second device buffer per slot. */
-typedef struct { const unsigned char *b; unsigned char *d_b; bc_dev *dev; } xor_op;
+typedef struct { const unsigned char *b; unsigned char *d_b; bc_dev *dev; int b_pageable; } xor_op;
 
 static int xor_chunk(void *arg, size_t idx, size_t off, size_t n, void *d, cudaStream_t st)
 {
@@ -1366,10 +1367,18 @@ static int xor_chunk(void *arg, size_t idx, size_t off, size_t n, void *d, cudaS
         BC_CUDA(cudaEventRecord(o->dev->e_h2d[sl], o->dev->s_h2d), "cudaEventRecord");
         BC_CUDA(cudaStreamWaitEvent(st, o->dev->e_h2d[sl], 0), "cudaStreamWaitEvent");
     } else {
-        /* host-in-the-loop pipeline: same stream as the kernel; for pageable memory the runtime
-         * stages the copy and keeps it ordered inside `st`.  (A plain cudaMemcpy would run on the
-         * legacy stream, which the non-blocking pipeline streams do not wait for.) */
-        BC_CUDA(cudaMemcpyAsync(d_b, o->b + off, n, cudaMemcpyHostToDevice, st), "cudaMemcpyAsync b");
+        /* host-in-the-loop pipeline: same stream as the kernel.  A pageable second operand is staged
+         * like the first one — through a pinned buffer of the slot, filled by the parallel copy pool
+         * (the runtime's own pageable path stages with one thread) — and the slot was retired before
+         * this chunk was issued, so its previous copy out of pin_b has completed. */
+        const unsigned char *src = o->b + off;
+        if (o->b_pageable) {
+            bc_slot *s = &o->dev->slot[sl];
+            if (!s->pin_b) BC_CUDA(cudaHostAlloc((void **)&s->pin_b, BC_CHUNK_BYTES, cudaHostAllocDefault), "cudaHostAlloc(staging b)");
+            par_memcpy(s->pin_b, src, n);
+            src = s->pin_b;
+        }
+        BC_CUDA(cudaMemcpyAsync(d_b, src, n, cudaMemcpyHostToDevice, st), "cudaMemcpyAsync b");
     }
     return bc_xor_dev(d, d_b, d, n, st);
 }
@@ -1395,8 +1404,10 @@ int bc_xor_host(const void *a, const void *b, void *out, size_t nbytes)
     if ((rc = dev_ensure_slots(d)) == BC_OK) {
         void *d_b = NULL;
         if ((rc = bc_scratch_get((void *)d, BC_SLOTS * BC_CHUNK_BYTES, &d_b)) == BC_OK) {
-            xor_op o = { (const unsigned char *)b, (unsigned char *)d_b, d };
-            rc = run_pipeline(d, (const unsigned char *)a, (unsigned char *)out, nbytes, BC_CHUNK_BYTES, xor_chunk, &o);
+            xor_op o = { (const unsigned char *)b, (unsigned char *)d_b, d, classify(b) == 0 };
+            size_t chunk = pick_chunk(nbytes, a, out);
+            if (o.b_pageable && chunk > g_pageable_chunk) chunk = g_pageable_chunk;
+            rc = run_pipeline(d, (const unsigned char *)a, (unsigned char *)out, nbytes, chunk, xor_chunk, &o);
         }
     }
     pthread_mutex_unlock(&d->lock);
@@ -1430,6 +1441,7 @@ int bc_shutdown(void)
                     cudaFree(s->d_buf);
                     if (s->pin_in) cudaFreeHost(s->pin_in);
                     if (s->pin_out) cudaFreeHost(s->pin_out);
+                    if (s->pin_b) cudaFreeHost(s->pin_b);
                     cudaStreamDestroy(s->stream);
                     cudaEventDestroy(s->done);
                     cudaEventDestroy(d->e_h2d[i]);
