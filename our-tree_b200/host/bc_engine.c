@@ -795,6 +795,31 @@ static int slot_retire(bc_slot *s)
     return BC_OK;
 }
 
+/* Size of pipeline chunk number `idx`, which starts at byte `off` of an nbytes transfer cut into
+ * granules of `chunk` bytes.  Without `ramp`: equal granules.  With it: 1/16, 1/8, 1/4, 1/2 granule,
+ * full granules (the last of them shortened to whole 4 KiB pages so that the tail fits exactly), then
+ * 1/2, 1/4, 1/8 and 1/16 granule plus any odd bytes.  Every chunk but the last is a multiple of
+ * 4096 bytes and none exceeds the granule.  Pure arithmetic (tests/c/host_san_test.c walks it). */
+size_t bc_internal_next_chunk(size_t nbytes, size_t off, size_t idx, size_t chunk, int ramp)
+{
+    size_t n = chunk;
+    const size_t left = nbytes - off;
+    if (ramp) {
+        const size_t q = chunk >> 4, tail_total = chunk - q;                 /* 1/2 + 1/4 + 1/8 + 1/16 */
+        if (idx < 4) {
+            n = chunk >> (4 - idx);
+        } else if (left > tail_total && ((left - tail_total) & ~(size_t)4095) > 0) {
+            n = (left - tail_total) & ~(size_t)4095;
+            if (n > chunk) n = chunk;
+        } else {
+            n = chunk >> 1;
+            while (n > q && left < 2 * n - q) n >>= 1;
+            if (n == q) n = left;
+        }
+    }
+    return n > left ? left : n;
+}
+
 /* One chunk's kernel: `d` holds n bytes that start at byte `off` of the caller's buffer. */
 typedef int (*chunk_fn)(void *arg, size_t chunk_idx, size_t off, size_t n, void *d, cudaStream_t st);
 
@@ -816,21 +841,7 @@ static int run_pipeline_enqueued(bc_dev *d, const unsigned char *in, unsigned ch
     const int ramp = tls_ramp && nbytes >= 8 * chunk && (chunk >> 4) >= ((size_t)1 << 20) && !getenv("BULKCIPHER_NO_RAMP");
     size_t n = 0;
     for (size_t off = 0; off < nbytes && rc == BC_OK; off += n, idx++) {
-        n = chunk;
-        if (ramp) {
-            const size_t left = nbytes - off, q = chunk >> 4, tail_total = chunk - q;   /* 1/2 + 1/4 + 1/8 + 1/16 */
-            if (idx < 4) {
-                n = chunk >> (4 - idx);                                  /* head: 1/16, 1/8, 1/4, 1/2 */
-            } else if (left > tail_total && ((left - tail_total) & ~(size_t)4095) > 0) {
-                n = (left - tail_total) & ~(size_t)4095;                 /* middle: full granules, then what is left of it */
-                if (n > chunk) n = chunk;
-            } else {
-                n = chunk >> 1;                                          /* tail: 1/2, 1/4, 1/8, 1/16 (+ the odd bytes) */
-                while (n > q && left < 2 * n - q) n >>= 1;
-                if (n == q) n = left;
-            }
-        }
-        if (n > nbytes - off) n = nbytes - off;
+        n = bc_internal_next_chunk(nbytes, off, idx, chunk, ramp);
         const int sl = (int)(idx % BC_SLOTS);
         bc_slot *s = &d->slot[sl];
         if (in) {

@@ -9,6 +9,7 @@
 #include <stdio.h>
 #include <stdlib.h>
 #include <string.h>
+#include <sys/mman.h>
 
 #include "aes.h"
 #include "aesni.h"
@@ -28,6 +29,8 @@ STUB(bc_arc4_batch_dev, size_t a, const void *b, unsigned c, size_t d, const voi
 STUB(bc_xor_dev, const void *a, const void *b, void *c, size_t d, void *e)
 
 void bc_internal_par_memcpy(void *dst, const void *src, size_t n);   /* host/bc_engine.c */
+size_t bc_internal_next_chunk(size_t nbytes, size_t off, size_t idx, size_t chunk, int ramp);   /* host/bc_engine.c */
+size_t bc_internal_read_ahead(unsigned char *dst, const unsigned char *src, size_t want);       /* host/aes_dropin.c */
 
 static int fails;
 #define CHECK(c) do { if (!(c)) { printf("FAIL %s:%d: %s\n", __FILE__, __LINE__, #c); fails++; } } while (0)
@@ -80,6 +83,50 @@ int main(void)
         CHECK(memcmp(dst + 1, src, n) == 0 && dst[0] == 0x5A && dst[n + 1] == 0x5A);
         free(src);
         free(dst);
+    }
+    /* the pipeline's chunk schedule: covers the transfer exactly, pages stay whole, no chunk above the granule */
+    {
+        const size_t M = (size_t)1 << 20, sizes[] = { 8 * 64 * M, 4096 * M, 1000 * M + 7, 8 * 64 * M + 4095, 8 * 64 * M + 4096 + 5, 513 * M, 128 * M, 16 };
+        for (unsigned k = 0; k < sizeof sizes / sizeof sizes[0]; k++)
+            for (int ramp = 0; ramp < 2; ramp++) {
+                const size_t chunk = k == 6 ? 16 * M : 64 * M;
+                size_t off = 0, idx = 0, first = 0, last = 0;
+                while (off < sizes[k]) {
+                    const size_t n = bc_internal_next_chunk(sizes[k], off, idx, chunk, ramp && sizes[k] >= 8 * chunk);
+                    CHECK(n > 0 && n <= chunk && (off + n == sizes[k] || n % 4096 == 0));
+                    if (n == 0) break;
+                    if (idx == 0) first = n;
+                    last = n;
+                    off += n; idx++;
+                }
+                CHECK(off == sizes[k]);
+                if (ramp && sizes[k] >= 8 * chunk) CHECK(first == chunk / 16 && last < chunk / 16 + 4096 && last >= chunk / 16);
+            }
+    }
+    /* the read-ahead copy of aes_crypt_ecb never faults: it stops at the first unreadable page */
+    {
+        unsigned char *m = mmap(NULL, 3 * 4096, PROT_READ | PROT_WRITE, MAP_PRIVATE | MAP_ANONYMOUS, -1, 0);
+        CHECK(m != MAP_FAILED);
+        for (int i = 0; i < 2 * 4096; i++) m[i] = (unsigned char)(i * 7 + 1);
+        CHECK(munmap(m + 2 * 4096, 4096) == 0);
+        unsigned char *dst = malloc(4 * 4096);
+        const size_t got = bc_internal_read_ahead(dst, m + 100, 4 * 4096);
+        CHECK(got == 0 || got == 2 * 4096 - 100);                 /* 0: process_vm_readv not permitted in this sandbox */
+        if (got) CHECK(memcmp(dst, m + 100, got) == 0);
+        CHECK(bc_internal_read_ahead(dst, m + 4096 - 8, 8) == 8 || got == 0);
+        free(dst);
+        munmap(m, 2 * 4096);
+        /* a block walk without a device: every call fails, nothing is written, nothing is cached */
+        if (bc_device_count() == 0) {
+            unsigned char in[16 * 8] = { 1 }, out[16 * 8];
+            memset(out, 0xCD, sizeof out);
+            for (int b = 0; b < 8; b++) CHECK(aes_crypt_ecb(&ctx, AES_ENCRYPT, in + 16 * b, out + 16 * b) != 0);
+            for (unsigned i = 0; i < sizeof out; i++) CHECK(out[i] == 0xCD);
+            CHECK(bc_aes_ecb_host_multi(1, (const uint32_t *)sched, 10, BC_ENCRYPT, in, out, sizeof in) != 0);
+            CHECK(bc_void_status() == 0);
+            AES_ECB_encrypt(in, out, sizeof in, sched, 14);
+            CHECK(bc_void_status() != 0 && out[0] == 0xCD);
+        }
     }
     printf(fails ? "host_san_test: %d failure(s)\n" : "host_san_test: ok\n", fails);
     return fails ? 1 : 0;
