@@ -442,6 +442,7 @@ def run_config5(pkg, L, rk, nr, st, ranks: Ranks, n_gpus: int, rank: int, steps:
     total = 256 * GIB
     shard = total // n_gpus
     free_b, _ = torch.cuda.mem_get_info()
+    free_b = int(ranks.reduce([free_b], "min")[0])                # one decision for all ranks (they meet at barriers below)
     in_place = 2 * shard > 0.92 * free_b
     if shard > 0.95 * free_b:
         return {"skipped": f"a {shard >> 30} GiB shard does not fit in {free_b >> 30} GiB of free HBM"}
