@@ -271,7 +271,8 @@ def run_reference(args):
         return 0
     threads = cpu_threads()
     t_all0 = time.perf_counter()
-    r = ReferenceCtr(SHARD_BYTES, threads)
+    # the whole 4 GiB-per-GPU workload per step (tests/test_bench_contract.py shrinks it through the environment)
+    r = ReferenceCtr(int(os.environ.get("BULKCIPHER_BENCH_REF_MIB", SHARD_BYTES >> 20)) << 20, threads)
     for _ in range(args.warmup):
         r.one_pass()
     t0 = time.perf_counter()
