@@ -838,7 +838,7 @@ static int run_pipeline_enqueued(bc_dev *d, const unsigned char *in, unsigned ch
      * travels out, and the other way round at the end — one link direction idles for a whole chunk at
      * each end.  Starting and finishing with chunks of 1/16, 1/8, 1/4, 1/2 of the granule shrinks
      * those two single-direction phases 16-fold. */
-    const int ramp = tls_ramp && nbytes >= 8 * chunk && (chunk >> 4) >= ((size_t)1 << 20) && !getenv("BULKCIPHER_NO_RAMP");
+    const int ramp = tls_ramp && nbytes >= 3 * chunk && (chunk >> 4) >= ((size_t)1 << 20) && !getenv("BULKCIPHER_NO_RAMP");
     size_t n = 0;
     for (size_t off = 0; off < nbytes && rc == BC_OK; off += n, idx++) {
         n = bc_internal_next_chunk(nbytes, off, idx, chunk, ramp);
