@@ -88,6 +88,30 @@ int main(void)
         free(a); free(b); bc_host_free(pa); bc_host_free(pb);
     }
 
+    /* device-resident buffers from C (no Python, no CUDA events): one call + sync, and 200 calls back to back */
+    {
+        const size_t dsizes[] = { 4096, 65536, 1 << 20, 4 << 20, 16 << 20, 64 << 20 };
+        void *d_in = bc_dev_alloc(64 << 20), *d_out = bc_dev_alloc(64 << 20);
+        if (!d_in || !d_out) { fprintf(stderr, "bc_dev_alloc failed: %s\n", bc_last_error()); return 1; }
+        printf("\nbc_aes_ctr_dev on device-resident buffers, called from C\n| bytes | one call + sync, us | per call, 200 back to back, us | GB/s back to back |\n|---|---|---|---|\n");
+        for (unsigned s = 0; s < sizeof dsizes / sizeof dsizes[0]; s++) {
+            const size_t n = dsizes[s];
+            double t[20];
+            for (int i = 0; i < 22; i++) {
+                const double t0 = now_us();
+                if (bc_aes_ctr_dev(rk, nr, counter, 128, 0, d_in, d_out, n, NULL, NULL) || bc_device_sync()) { fprintf(stderr, "%s\n", bc_last_error()); return 1; }
+                if (i >= 2) t[i - 2] = now_us() - t0;
+            }
+            qsort(t, 20, sizeof t[0], cmp);
+            const double t0 = now_us();
+            for (int i = 0; i < 200; i++) bc_aes_ctr_dev(rk, nr, counter, 128, 0, d_in, d_out, n, NULL, NULL);
+            bc_device_sync();
+            const double per = (now_us() - t0) / 200;
+            printf("| %zu | %.1f | %.2f | %.1f |\n", n, t[10], per, n / per / 1e3);
+        }
+        bc_dev_free(d_in); bc_dev_free(d_out);
+    }
+
     /* the reference's "Plain ECB" loop, one aes_crypt_ecb call per 16 bytes (aes-modes/test.c:37-41) */
     {
         const size_t n = 16 << 20;
