@@ -209,6 +209,16 @@ rc4_batch_kernel(const __grid_constant__ Rc4Args a)
  * this step's swap lands on it, which halves the dependent chain per byte.
  * ==================================================================== */
 
+/* How a warp's 32 x 64-byte box meets the data: IO_LOAD = TMA-load the input box, XOR in shared memory,
+ * TMA-store (out of place); IO_XOR = in == out, store the keystream box and let the TMA unit XOR it into
+ * HBM; IO_KS = no input, the keystream itself is the output (arc4_prep).  A template parameter, so each
+ * case is straight-line code (round 2: shared-memory reductions instead of LDS.128 + STS.128 for IO_LOAD
+ * were tried and lose, 1 269 vs 1 354 GB/s). */
+enum { IO_LOAD = 0, IO_XOR = 1, IO_KS = 2 };
+#ifndef BC_RC4_CUNROLL
+#define BC_RC4_CUNROLL 4      /* 16-byte chunks of a 64-byte slab unrolled in the PRGA loop (A/B knob) */
+#endif
+constexpr int kCUnroll = BC_RC4_CUNROLL;
 constexpr int kTmaWarps    = kRc4Threads / 32;
 constexpr int kTmaStageOff = kRc4Smem;              /* [warp][2][kBoxBytes] */
 constexpr int kTmaBarOff   = kTmaStageOff + kTmaWarps * 2 * kBoxBytes;
@@ -249,7 +259,7 @@ __device__ __forceinline__ uint32_t prga_next(Prga &p, uint32_t base, uint32_t b
     return k;
 }
 
-template <bool KEY16>
+template <bool KEY16, int IO>
 __global__ void __launch_bounds__(kRc4Threads, 2)
 rc4_batch_tma_kernel(const __grid_constant__ Rc4TmaArgs a, const __grid_constant__ CUtensorMap tm_in,
                      const __grid_constant__ CUtensorMap tm_out)
@@ -278,7 +288,7 @@ rc4_batch_tma_kernel(const __grid_constant__ Rc4TmaArgs a, const __grid_constant
         const uint32_t row0 = (uint32_t)(sg * 32);
 
         /* first box on its way while the key schedule runs */
-        if (a.has_in && !a.xor_in_place && n_slabs && lane == 0) {
+        if (IO == IO_LOAD && n_slabs && lane == 0) {
             mbar_expect_tx(bar, kBoxBytes);
             tma_load_2d(stage, &tm_in, 0, row0, bar);
         }
@@ -333,15 +343,15 @@ rc4_batch_tma_kernel(const __grid_constant__ Rc4TmaArgs a, const __grid_constant
             const uint32_t sbuf = stage + buf * kBoxBytes;
             if (lane == 0 && k + 1 < n_slabs) {
                 tma_store_wait_read();               /* the other buffer's last store has left shared memory */
-                if (a.has_in && !a.xor_in_place) {
+                if (IO == IO_LOAD) {
                     mbar_expect_tx(bar + 8 * (buf ^ 1u), kBoxBytes);
                     tma_load_2d(stage + (buf ^ 1u) * kBoxBytes, &tm_in, (k + 1) * kSlab, row0, bar + 8 * (buf ^ 1u));
                 }
             }
             __syncwarp();
-            if (a.has_in && !a.xor_in_place) { mbar_wait(bar + 8 * buf, (phases >> buf) & 1u); phases ^= 1u << buf; }
+            if (IO == IO_LOAD) { mbar_wait(bar + 8 * buf, (phases >> buf) & 1u); phases ^= 1u << buf; }
             const uint32_t valid = (uint32_t)(a.length - (uint64_t)k * kSlab < kSlab ? a.length - (uint64_t)k * kSlab : kSlab);
-#pragma unroll
+#pragma unroll (kCUnroll)
             for (uint32_t c = 0; c < 4; c++) {
                 if (c * 16 < valid) {                /* length is a multiple of 16: whole chunks only */
                     uint32_t w[4];
@@ -354,16 +364,19 @@ rc4_batch_tma_kernel(const __grid_constant__ Rc4TmaArgs a, const __grid_constant
                         w[q] = acc;
                     }
                     const uint32_t sa = sbuf + row_off + ((c ^ swz) << 4);
-                    uint4 d = make_uint4(0, 0, 0, 0);
-                    if (a.has_in && !a.xor_in_place) d = lds128(sa);
-                    d.x ^= w[0]; d.y ^= w[1]; d.z ^= w[2]; d.w ^= w[3];
-                    sts128(sa, d);
+                    if (IO == IO_LOAD) {
+                        uint4 d = lds128(sa);
+                        d.x ^= w[0]; d.y ^= w[1]; d.z ^= w[2]; d.w ^= w[3];
+                        sts128(sa, d);
+                    } else {
+                        sts128(sa, make_uint4(w[0], w[1], w[2], w[3]));      /* keystream only (IO_XOR: the TMA unit XORs it into HBM) */
+                    }
                 }
             }
             asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
             __syncwarp();
             if (lane == 0) {
-                if (a.xor_in_place) tma_reduce_xor_2d(&tm_out, k * (kSlab / 4), row0, sbuf);
+                if (IO == IO_XOR) tma_reduce_xor_2d(&tm_out, k * (kSlab / 4), row0, sbuf);
                 else tma_store_2d(&tm_out, k * kSlab, row0, sbuf);
             }
         }
@@ -381,10 +394,10 @@ rc4_batch_tma_kernel(const __grid_constant__ Rc4TmaArgs a, const __grid_constant
     if (lane == 0) tma_store_wait_all();
 }
 
-template <bool KEY16>
+template <bool KEY16, int IO>
 int launch_rc4_tma(const Rc4TmaArgs &a, const CUtensorMap &tin, const CUtensorMap &tout, cudaStream_t st)
 {
-    int rc = set_smem<rc4_batch_tma_kernel<KEY16>>(kTmaSmem);
+    int rc = set_smem<rc4_batch_tma_kernel<KEY16, IO>>(kTmaSmem);
     if (rc) return rc;
     const int sms = bc_cached_sm_count();
     if (sms <= 0) return BC_ERR_CUDA;
@@ -392,7 +405,7 @@ int launch_rc4_tma(const Rc4TmaArgs &a, const CUtensorMap &tin, const CUtensorMa
     const uint64_t ctas = (groups + kTmaWarps - 1) / kTmaWarps;
     const uint64_t cap = (uint64_t)sms * 2;
     const int grid = (int)(ctas < cap ? ctas : cap);
-    rc4_batch_tma_kernel<KEY16><<<grid, kRc4Threads, kTmaSmem, st>>>(a, tin, tout);
+    rc4_batch_tma_kernel<KEY16, IO><<<grid, kRc4Threads, kTmaSmem, st>>>(a, tin, tout);
     BC_CUDA(cudaGetLastError(), "rc4_batch_tma_kernel launch");
     return BC_OK;
 }
@@ -471,7 +484,11 @@ extern "C" int bc_arc4_batch_dev(size_t n_streams, const void *d_keys, unsigned 
         int rc = make_row_tensor_map(&tout, d_out, n_streams, length, t.xor_in_place != 0);
         if (rc) return rc;
         if ((rc = make_row_tensor_map(&tin, d_in ? d_in : d_out, n_streams, length))) return rc;
-        return key16 ? launch_rc4_tma<true>(t, tin, tout, st) : launch_rc4_tma<false>(t, tin, tout, st);
+        const int io = !t.has_in ? IO_KS : t.xor_in_place ? IO_XOR : IO_LOAD;
+        if (key16) return io == IO_LOAD ? launch_rc4_tma<true, IO_LOAD>(t, tin, tout, st)
+                        : io == IO_XOR ? launch_rc4_tma<true, IO_XOR>(t, tin, tout, st) : launch_rc4_tma<true, IO_KS>(t, tin, tout, st);
+        return io == IO_LOAD ? launch_rc4_tma<false, IO_LOAD>(t, tin, tout, st)
+             : io == IO_XOR ? launch_rc4_tma<false, IO_XOR>(t, tin, tout, st) : launch_rc4_tma<false, IO_KS>(t, tin, tout, st);
     }
     if (vec) return key16 ? launch_rc4<true, true>(a, st) : launch_rc4<true, false>(a, st);
     return key16 ? launch_rc4<false, true>(a, st) : launch_rc4<false, false>(a, st);
